@@ -1,0 +1,191 @@
+/* libjrl_lbm.so -- C ABI of the B200-native D2Q9 lattice update (sm_100a).
+ *
+ * This is the drop-in boundary for JRL-LBM's per-step hot path.  Every entry point replaces
+ * one of the reference's pybind/TORCH_LIBRARY functions or one chain of torch ops inside a
+ * solver-object method (reference file:line cited per function, relative to the reference
+ * tree).  Conventions (reference: propagation.cu:66-72):
+ *
+ *   - all pointers are DEVICE pointers owned by the caller; the library never allocates or
+ *     frees user-visible memory and never synchronises the stream;
+ *   - layout [B, C, H, W] contiguous, fp32; flags uint8 [B,1,H,W];
+ *     f/h: C = 9, rho/C/phi_obs: C = 1, vel/force/mesh_grid/obs_vel: C = 2 (channel 0 = x);
+ *   - optional tensors are NULL (the reference passes empty tensors, propagation.cu:513-517);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - return value 0 = success, negative = error; jrl_last_error() returns the message of
+ *     the calling thread's last failure.
+ *
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with
+ * JRL_ERR_CUDA.
+ */
+#ifndef JRL_LBM_H
+#define JRL_LBM_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define JRL_LBM_VERSION 100
+
+enum { JRL_OK = 0, JRL_ERR_ARG = -1, JRL_ERR_CUDA = -2 };
+
+/* utils/types.py:5-23, 69-73 */
+enum { JRL_CELL_NOTHING = 0, JRL_CELL_FLUID = 1, JRL_CELL_OBSTACLE = 2, JRL_CELL_EMPTY = 4,
+       JRL_CELL_INFLOW = 8, JRL_CELL_OUTFLOW = 16, JRL_CELL_INFLOW_2 = 32 };
+enum { JRL_AXI_NOT = 0, JRL_AXI_X = 1, JRL_AXI_Y = 2 };
+enum { JRL_OP_BGK = 0, JRL_OP_MRT = 1, JRL_OP_KBC = 2 };
+enum { JRL_KBC_LBGK = 0, JRL_KBC_A = 0x85, JRL_KBC_B = 0x86, JRL_KBC_C = 0x89, JRL_KBC_D = 0x8A };
+
+int jrl_version(void);
+const char *jrl_last_error(void);
+
+/* ---- R1: streaming with all link-wise boundary rules --------------------------------------
+ * Replaces propagation.propagation_2d_forward (propagation.cpp:15-33 -> propagation.cu:490-524,
+ * kernel :22-488) AND the wrapper's `f_new = f + 0.0` copy (LBM_propagation_2d.py:49): f_new is
+ * fully written, it need not be initialised.  rho / vel are mutated in place at INFLOW and
+ * INFLOW_2 cells exactly as the reference does (propagation.cu:300, 320-321, 362).
+ * inflow_density < 0 means "none" (LBM_propagation_2d.py:61-62); inflow_vel is a device [2].
+ * OUTFLOW cells copy their inward neighbour's post-stream populations (the reference has a
+ * data race there, propagation.cu:250-254; this is the deterministic reading). */
+int jrl_stream_f32(const uint8_t *flags, const float *f, const float *phi_obs, float *f_new,
+                   float *rho, float *vel, const float *inflow_vel, double inflow_density,
+                   int axisym, int B, int H, int W, void *stream);
+
+/* prop.rebounce_obstacle, LBM_propagation_2d.py:181-186 */
+int jrl_rebounce_f32(const float *f, const uint8_t *flags, float *f_new, int B, int H, int W, void *stream);
+
+/* ---- R2 / R7: moments ---------------------------------------------------------------------
+ * jrl_moments_f32 replaces the torch-op chain of LBMMacroCompute2d.macro_compute
+ * (LBM_macro_compute_2d.py:316-351) including contact_angle_correctness (:237-271) when
+ * use_contact != 0 (contact_tan = tan(pi/2 - contact_angle) as fp32).  `c` = dx/dt.
+ * rho_new/vel_new must not alias rho_old/vel_old. */
+int jrl_moments_f32(const float *f, const float *rho_old, const float *vel_old, const uint8_t *flags,
+                    float *rho_new, float *vel_new, int use_contact, float contact_tan, double c,
+                    int B, int H, int W, void *stream);
+/* macro_compute.macro_compute_2d_forward (macro_compute.cpp:43-60, kernel macro_compute.cu:80-157) */
+int jrl_moments_kernel_f32(const float *f, const float *rho_old, const float *vel_old, const uint8_t *flags,
+                           float *rho_new, float *vel_new, double c, int B, int H, int W, void *stream);
+/* LBMMacroCompute2d.macro_compute_C (LBM_macro_compute_2d.py:273-295); clamp01 != 0 fuses the
+ * demo's torch.clamp(C, 0, 1) (demo_2d_LBM_JRL_C_cylinder.py:324) */
+int jrl_moments_C_f32(const float *h, const float *C_old, const uint8_t *flags, float *C_new, int clamp01,
+                      int B, int H, int W, void *stream);
+/* macro_compute.macro_compute_C_2d_forward (macro_compute.cpp:29-41, kernel macro_compute.cu:22-78) */
+int jrl_moments_C_kernel_f32(double dt, const float *h, const float *C_old, const uint8_t *flags,
+                             const float *vel, const float *mesh_grid, float *C_new, int axisym,
+                             int B, int H, int W, void *stream);
+
+/* ---- R3: equilibrium, LBMCollision2d.get_feq_static_ (LBM_collision_2d.py:236-263) ---------- */
+int jrl_feq_f32(const float *rho, const float *vel, const float *force, float *feq, double dx, double dt,
+                int B, int H, int W, void *stream);
+
+/* ---- R6: 9-point stencils, collision_2d.get_grad_2d_forward / get_div_2d_forward
+ * (collision_2d.cpp:32-50, kernels collision_2d.cu:22-220) ------------------------------------ */
+int jrl_grad_f32(const float *s, const uint8_t *flags, float *grad, double dx, int axisym,
+                 int B, int H, int W, void *stream);
+int jrl_div_f32(const float *v, const uint8_t *flags, float *div, double dx, int axisym,
+                int B, int H, int W, void *stream);
+
+/* ---- R4 / R4m / R4k / R6: collision ----------------------------------------------------------
+ * One launch replaces LBMCollision2d.collision (LBM_collision_2d.py:473-555),
+ * LBMCollisionMRT2d.collision (LBM_collision_MRT_2d.py:121-184) or LBMCollisionKBC2d.collision
+ * (LBM_collision_KBC_2d.py:251-317), including get_feq_, the half-force velocity shift and the
+ * axisymmetric source get_G_source_from_axisymmetric (LBM_collision_2d.py:343-471) with its
+ * four gradient and one divergence stencils evaluated in registers. */
+typedef struct jrl_collide_desc
+{
+    int B, H, W;
+    int axisym;           /* JRL_AXI_* */
+    int op;               /* JRL_OP_* */
+    int kbc_type;         /* JRL_KBC_* (op == JRL_OP_KBC) */
+    int is_convection;    /* BGK only */
+    double dx, dt;
+    double tau;           /* relaxation time used by the operator (tau_D when is_convection) */
+    const float *mrt;     /* HOST pointer to the 81 fp32 entries of M^-1 S M (op == JRL_OP_MRT) */
+    const float *f;       /* [B,9,H,W] post-stream populations */
+    const float *rho;     /* [B,1,H,W] */
+    const float *vel;     /* [B,2,H,W] */
+    const uint8_t *flags; /* [B,1,H,W] */
+    const float *force;   /* [B,2,H,W] or NULL */
+    const float *mesh_grid; /* [B,2,H,W] (cell centres) or NULL; required when axisym != 0 */
+    float *f_out;         /* [B,9,H,W]; may alias f when axisym == 0 or is_convection */
+} jrl_collide_desc;
+int jrl_collide_f32(const jrl_collide_desc *d, void *stream);
+
+/* ---- R5: regularised moving-wall reconstruction ----------------------------------------------
+ * solid_fluid_coupling.solve_obstacle_2d_forward (solid_fluid_coupling.cpp:17-38 ->
+ * solid_fluid_coupling.cu:254-290, kernel :25-252).  f_new is fully written. */
+int jrl_wall_f32(double dt, double dx, double tau, const float *vel, const uint8_t *flags, const float *f,
+                 float *f_new, const float *phi_obs, const float *obs_vel, int axisym,
+                 int B, int H, int W, void *stream);
+
+/* ---- R8: strip reductions feeding the validation plots ---------------------------------------
+ * out[0] = sum_k ((C[y0,k]-C[y0-1,k]) + (r[k+1]C[y0,k+1]-r[k]C[y0,k])/r[k]) * area[k], k < ncol
+ *          (demo_2d_LBM_JRL_C_cylinder.py:344-348, 355-359), r = mesh_grid[0,0,y0,:]
+ * out[1] = sum_k C[y0,k] * area[k]   (:239-241; demo_2d_LBM_JRL_C_45degree.py:353-376)
+ * area[k] = pi((k+1)^2 - k^2) (:176-180).  One warp, shuffle reduction; batch element 0. */
+int jrl_strip_flux_f32(const float *C, const float *mesh_grid, int y0, int ncol, float *out2,
+                       int H, int W, void *stream);
+
+/* ---- R9 (extension; absent from the reference): momentum-exchange force on OBSTACLE cells.
+ * out2[0..1] += sum over non-obstacle cells x and links q with x+e_q OBSTACLE of 2 e_q f_q(x)
+ * (post-collision f).  out2 must be zeroed by the caller. */
+int jrl_momentum_exchange_f32(const float *f_post, const uint8_t *flags, double *out2,
+                              int B, int H, int W, void *stream);
+
+/* ---- fused step: stream + boundaries + moments + collide in one pass ---------------------------
+ * Semantically identical (bit for bit) to jrl_stream_f32 -> [jrl_wall_f32] -> jrl_moments_f32 /
+ * jrl_moments_C_f32 -> jrl_collide_f32 on the same inputs, for the cases where the collision
+ * is local: axisym == 0, or is_convection (the axisymmetric FLUID source needs post-stream
+ * moments of neighbours and stays a two-launch path).  Pull scheme, double-buffered:
+ * f_in -> f_out, 9 fp32 reads + 9 fp32 writes per cell (72 B per lattice update). */
+typedef struct jrl_step_desc
+{
+    int B, H, W;
+    int axisym;
+    int op, kbc_type, is_convection;
+    int use_contact;        /* fluid: contact-angle wall density on OBSTACLE cells of rho_out */
+    float contact_tan;
+    int clamp01;            /* concentration: clamp C to [0,1] before the collision */
+    double dx, dt, tau;
+    const float *mrt;       /* HOST pointer, 81 floats */
+    const uint8_t *flags;
+    const float *f_in;
+    float *f_out;           /* must not alias f_in */
+    const float *phi_obs;   /* NULL: halfway bounce-back */
+    float *rho;             /* in/out: previous-step density (kept at OBSTACLE cells, read at INFLOW).
+                               NULL allowed when no cell needs it (all FLUID) */
+    float *vel;             /* in/out likewise; read-only input when is_convection */
+    float *rho_out;         /* NULL: moments are not stored (pure 72 B/LUP path) */
+    float *vel_out;
+    const float *force;     /* [B,2,H,W] or NULL */
+    const float *mesh_grid;
+    const float *inflow_vel;
+    double inflow_density;  /* < 0: none */
+    /* moving wall (R5) between streaming and moments; needs phi_obs and the previous-step vel */
+    int use_wall;
+    const float *obs_vel;
+    /* Multi-GPU row slab.  slab_rows == 0: every plane holds the whole grid [H, W].
+       slab_rows > 0: every plane (f, flags, phi, rho, vel, force, mesh, obs_vel, outputs) is a
+       local [slab_rows + 2, W] array holding global rows slab_row0 .. slab_row0+slab_rows-1 in
+       local rows 1 .. slab_rows; local rows 0 and slab_rows+1 are ghost rows the caller fills
+       by halo exchange (the periodic wrap of FLUID cells makes the rank topology a ring). */
+    int slab_row0, slab_rows;
+    /* Global rows [row_begin, row_end) updated by this launch (lets the caller update the
+       slab's edge rows first, start the halo exchange, then update the interior);
+       row_begin == row_end == 0: all stored rows. */
+    int row_begin, row_end;
+    int force_vec;          /* 0 = widest cells-per-thread the extents/alignment allow; 1, 2, 4 */
+} jrl_step_desc;
+int jrl_step_f32(const jrl_step_desc *d, void *stream);
+
+/* ---- row-slab halo helpers (multi-GPU) ----------------------------------------------------------
+ * Pack / unpack `nrows` full rows of all C planes of a [C,Hloc,W] slab starting at row `row`
+ * into a contiguous [C,nrows,W] staging buffer (the message NCCL sends to the neighbour rank). */
+int jrl_halo_pack_f32(const float *field, float *staging, int C, int Hloc, int W, int row, int nrows, void *stream);
+int jrl_halo_unpack_f32(float *field, const float *staging, int C, int Hloc, int W, int row, int nrows, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* JRL_LBM_H */

@@ -1,0 +1,560 @@
+// D2Q9 lattice constants, neighbour rules and per-cell arithmetic shared by every kernel of
+// libjrl_lbm.so (sm_100a only).
+//
+// Everything here is `__device__ __forceinline__` and works on registers; the kernels in
+// ops.cu (one reference operator per launch) and fused.cu (stream + boundaries + moments +
+// collide in one pass) are built from these pieces, so the fused path and the per-operator
+// path compute bit-identical results.
+//
+// Arithmetic contract: fp32 storage; every expression keeps the operation ORDER of the
+// reference's path (cited per function, paths relative to the reference tree) and fp64
+// intermediates exactly where the reference's C++ literals force them.  The library is built
+// with -fmad=false, so the only fused multiply-adds are the ones written as fmaf() here.
+#pragma once
+#include <cstdint>
+#ifndef JRL_MRT_FMA
+#define JRL_MRT_FMA 0  // 1: contract the 9x9 MRT matvec into FMAs (faster, not bit-equal to the oracle)
+#endif
+#include <cuda_runtime.h>
+
+namespace jrl {
+
+// utils/types.py:5-15 -- compared with ==, never as bit sets.
+enum : uint8_t { CT_NOTHING = 0, CT_FLUID = 1, CT_OBSTACLE = 2, CT_EMPTY = 4, CT_INFLOW = 8, CT_OUTFLOW = 16, CT_INFLOW_2 = 32 };
+enum : int { AXI_NOT = 0, AXI_X = 1, AXI_Y = 2 };
+// utils/types.py:18-23
+enum : int { KBC_LBGK = 0, KBC_A = 0x85, KBC_B = 0x86, KBC_C = 0x89, KBC_D = 0x8A };
+enum : int { OP_BGK = 0, OP_MRT = 1, OP_KBC = 2 };
+
+// propagation.cu:9-20, 49-64: rest, +x, +y, -x, -y, ++, -+, --, +-
+#define JRL_EX(q) ((q) == 1 || (q) == 5 || (q) == 8 ? 1 : ((q) == 3 || (q) == 6 || (q) == 7 ? -1 : 0))
+#define JRL_EY(q) ((q) == 2 || (q) == 5 || (q) == 6 ? 1 : ((q) == 4 || (q) == 7 || (q) == 8 ? -1 : 0))
+
+__device__ __forceinline__ constexpr int opp(int q)
+{
+    return q == 0 ? 0 : (q <= 4 ? ((q + 1) % 4) + 1 : ((q - 3) % 4) + 5);  // {0,3,4,1,2,7,8,5,6}
+}
+__device__ __forceinline__ constexpr int mirror_x(int q)
+{
+    // {0,3,2,1,4,6,5,8,7}
+    return q == 1 ? 3 : q == 3 ? 1 : q == 5 ? 6 : q == 6 ? 5 : q == 7 ? 8 : q == 8 ? 7 : q;
+}
+__device__ __forceinline__ constexpr int mirror_y(int q)
+{
+    // {0,1,4,3,2,8,7,6,5}
+    return q == 2 ? 4 : q == 4 ? 2 : q == 5 ? 8 : q == 8 ? 5 : q == 6 ? 7 : q == 7 ? 6 : q;
+}
+__device__ __forceinline__ constexpr float weight(int q)
+{
+    return q == 0 ? (float)(4.0 / 9.0) : (q <= 4 ? (float)(1.0 / 9.0) : (float)(1.0 / 36.0));
+}
+
+// One batch element's view of the lattice.  Plane stride is 64-bit: 9*H*W exceeds 2^31 at
+// 32768^2 (the reference's int indexing overflows there, propagation.cu:38, 66-72).
+//
+// Row-slab storage (multi-GPU): a rank stores global rows [y_off, y_off + Hloc) of every plane as
+// local rows 1..Hloc of a [Hloc + 2, W] plane; local rows 0 and Hloc + 1 are ghost rows filled by
+// the halo exchange.  H, W stay the GLOBAL extents, so every neighbour rule (periodic wrap of
+// FLUID cells, mirror / clamp at the domain edge) is evaluated in global coordinates, and
+// cell() maps the result -- always within one row of the current cell, modulo H -- to storage.
+struct Grid
+{
+    int H, W;
+    int axisym;
+    long long HW;  // plane stride in elements: H*W, or (Hloc+2)*W for a slab
+    int slab;      // 0: whole grid stored
+    int y_off;     // slab: global row of local row 1
+};
+
+// Storage index of cell (sy, sx), a neighbour (or self) of the cell in global row y.
+__device__ __forceinline__ long long cell(const Grid &g, int y, int sy, int sx)
+{
+    int row = sy;
+    if (g.slab)
+    {
+        int d = sy - y;
+        if (d > 1)
+            d -= g.H;
+        else if (d < -1)
+            d += g.H;
+        row = y - g.y_off + 1 + d;
+    }
+    return (long long)row * g.W + sx;
+}
+
+// Neighbour coordinates of one cell.
+//   mirror = true : streaming rule, propagation.cu:74-87 (FLUID wraps, others mirror to 1 / W-2)
+//   mirror = false: stencil / wall rule, collision_2d.cu:59-72, solid_fluid_coupling.cu:98-112
+struct Nbr
+{
+    int xn, xp, yn, yp;
+    bool on_x, on_y;
+};
+
+template <bool MIRROR>
+__device__ __forceinline__ Nbr neighbours(const Grid &g, uint8_t me, int y, int x)
+{
+    Nbr n;
+    const bool fluid = me == CT_FLUID;
+    n.on_x = (x == 0) && g.axisym == AXI_X;
+    n.on_y = (y == 0) && g.axisym == AXI_Y;
+    int xn_o, xp_o, yn_o, yp_o;
+    if (MIRROR)
+    {
+        xn_o = x - 1 < 0 ? 1 : x - 1;
+        xp_o = x + 1 >= g.W ? g.W - 2 : x + 1;
+        yn_o = y - 1 < 0 ? 1 : y - 1;
+        yp_o = y + 1 >= g.H ? g.H - 2 : y + 1;
+    }
+    else
+    {
+        xn_o = max(0, x - 1);
+        xp_o = min(g.W - 1, x + 1);
+        yn_o = max(0, y - 1);
+        yp_o = min(g.H - 1, y + 1);
+    }
+    n.xn = n.on_x ? 0 : (fluid ? (x == 0 ? g.W - 1 : x - 1) : xn_o);
+    n.xp = fluid ? (x + 1 == g.W ? 0 : x + 1) : xp_o;
+    n.yn = n.on_y ? 0 : (fluid ? (y == 0 ? g.H - 1 : y - 1) : yn_o);
+    n.yp = fluid ? (y + 1 == g.H ? 0 : y + 1) : yp_o;
+    return n;
+}
+
+// Upstream ("income") and downstream ("outcome") cell of direction q, propagation.cu:88-108.
+__device__ __forceinline__ long long income(const Grid &g, const Nbr &n, int y, int x, int q)
+{
+    const int ex = JRL_EX(q), ey = JRL_EY(q);
+    const int sx = ex > 0 ? n.xn : (ex < 0 ? n.xp : x);
+    const int sy = ey > 0 ? n.yn : (ey < 0 ? n.yp : y);
+    return cell(g, y, sy, sx);
+}
+__device__ __forceinline__ long long outcome(const Grid &g, const Nbr &n, int y, int x, int q)
+{
+    const int ex = JRL_EX(q), ey = JRL_EY(q);
+    const int sx = ex > 0 ? n.xp : (ex < 0 ? n.xn : x);
+    const int sy = ey > 0 ? n.yp : (ey < 0 ? n.yn : y);
+    return cell(g, y, sy, sx);
+}
+
+// ------------------------------------------------------------------------------------------
+// R1: pull streaming of one cell with every link rule except the INFLOW / INFLOW_2 / OUTFLOW
+// overwrites (propagation.cu:110-193).  f, fl, phi are batch-element bases.
+// ------------------------------------------------------------------------------------------
+template <bool HAS_PHI>
+__device__ __forceinline__ void stream_links(const Grid &g, const float *__restrict__ f,
+                                             const uint8_t *__restrict__ fl, const float *__restrict__ phi,
+                                             int y, int x, uint8_t me, float out[9])
+{
+    const Nbr n = neighbours<true>(g, me, y, x);
+    const long long self = cell(g, y, y, x);
+    out[0] = f[self];
+    const float t = HAS_PHI ? phi[self] : 0.f;
+#pragma unroll
+    for (int q = 1; q < 9; ++q)
+    {
+        int qi = q;  // income_Q_idx: axis-crossing links read the mirrored population
+        if (n.on_x && (q == 5 || q == 8 || q == 1))
+            qi = mirror_x(q);
+        else if (n.on_y && (q == 5 || q == 6 || q == 2))
+            qi = mirror_y(q);
+        const long long src = income(g, n, y, x, q);
+        const float pulled = f[qi * g.HW + src];
+        if (me == CT_OBSTACLE)
+        {
+            out[opp(q)] = pulled;  // solid cells store the reflected incoming set (:111-128)
+            continue;
+        }
+        if (fl[src] != CT_OBSTACLE)
+        {
+            out[q] = pulled;
+            continue;
+        }
+        const float f_this = f[opp(q) * g.HW + self];
+        float v = f_this;  // halfway bounce-back (:155-159)
+        if (HAS_PHI)
+        {
+            if (t >= 0.5f && t <= 1.f)
+            {
+                const float t1 = 2.f * t - 1.f;
+                v = t1 * pulled + (1.f - t1) * f_this;  // :163-169
+            }
+            else if (t <= 0.5f && t >= 0.f)
+            {
+                int qo = q;
+                if (n.on_x && (q == 6 || q == 7 || q == 3))
+                    qo = mirror_x(q);
+                else if (n.on_y && (q == 7 || q == 8 || q == 4))
+                    qo = mirror_y(q);
+                const float t2 = 2.f * t;
+                const float f_next = f[opp(qo) * g.HW + outcome(g, n, y, x, q)];
+                v = t2 * f_this + (1.f - t2) * f_next;  // :170-184
+            }
+        }
+        out[q] = v;
+    }
+}
+
+// Equilibrium of the INFLOW / INFLOW_2 reset with the reference kernel's mixed precision
+// (propagation.cu:340-350): cs2, uv, eu fp32; `1.0 + eu / cs2` and the second-order term fp64;
+// each of the two statements rounds to fp32 on store.
+__device__ __forceinline__ void inflow_equilibrium(float rho_t, float ux, float uy, float out[9])
+{
+    const float cs2 = (float)(1.0 / 3.0);
+    const float uv = ux * ux + uy * uy;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+    {
+        const float eu = ux * (float)JRL_EX(q) + uy * (float)JRL_EY(q);
+        const float rw = rho_t * weight(q);
+        const float first = (float)((double)rw * (1.0 + (double)(eu / cs2)));
+        const double second = (double)rw * (0.5 * (double)eu * (double)eu / (double)cs2 / (double)cs2 - 0.5 * (double)uv / (double)cs2);
+        out[q] = (float)((double)first + second);
+    }
+}
+
+// Inflow description of one streaming call (LBM_propagation_2d.py:52-62).
+struct Inflow
+{
+    float *rho;               // [B,1,H,W] or null; written at INFLOW (if density >= 0) and INFLOW_2
+    float *vel;               // [B,2,H,W] or null; written at INFLOW when inflow_vel is given
+    const float *inflow_vel;  // device [2] or null
+    float density;            // < 0: none
+    int has_density;
+};
+
+// Streaming of one cell followed by its INFLOW / INFLOW_2 reset (propagation.cu:295-377).
+// `rho_b`, `vel_b` are this batch element's bases inside in.rho / in.vel (or null).
+// WRITE = false evaluates the same values without the rho/vel side effects (used when an
+// OUTFLOW cell re-evaluates its inward neighbour).
+template <bool HAS_PHI, bool WRITE>
+__device__ __forceinline__ void stream_with_inflow(const Grid &g, const float *__restrict__ f,
+                                                   const uint8_t *__restrict__ fl, const float *__restrict__ phi,
+                                                   const Inflow &in, float *rho_b, float *vel_b, int y, int x,
+                                                   float out[9])
+{
+    const long long self = cell(g, y, y, x);
+    const uint8_t me = fl[self];
+    if (me == CT_INFLOW)
+    {
+        float rho_t = 0.f;
+        if (rho_b != nullptr && in.has_density)
+        {
+            rho_t = in.density;
+            if (WRITE)
+                rho_b[self] = rho_t;
+        }
+        else if (rho_b != nullptr)
+            rho_t = rho_b[self];
+        else if (in.has_density)
+            rho_t = in.density;
+        float ux = 0.f, uy = 0.f;
+        if (vel_b != nullptr && in.inflow_vel != nullptr)
+        {
+            ux = in.inflow_vel[0];
+            uy = in.inflow_vel[1];
+            if (WRITE)
+            {
+                vel_b[self] = ux;
+                vel_b[g.HW + self] = uy;
+            }
+        }
+        else if (vel_b != nullptr)
+        {
+            ux = vel_b[self];
+            uy = vel_b[g.HW + self];
+        }
+        else if (in.inflow_vel != nullptr)
+        {
+            ux = in.inflow_vel[0];
+            uy = in.inflow_vel[1];
+        }
+        inflow_equilibrium(rho_t, ux, uy, out);
+        return;
+    }
+    if (me == CT_INFLOW_2)
+    {
+        const float ux = vel_b == nullptr ? 0.f : vel_b[self];
+        const float uy = vel_b == nullptr ? 0.f : vel_b[g.HW + self];
+        if (WRITE && rho_b != nullptr)
+            rho_b[self] = 1.f;
+        inflow_equilibrium(1.f, ux, uy, out);
+        return;
+    }
+    stream_links<HAS_PHI>(g, f, fl, phi, y, x, me, out);
+}
+
+// Complete streaming of one cell including the OUTFLOW copy (propagation.cu:195-255).  The
+// reference reads the neighbour's f_new while another thread writes it; here, as in the
+// oracle, the value is defined as the neighbour's populations after streaming and inflow
+// reset.  (The neighbour's own OUTFLOW copy, if it is one, is not chained.)
+template <bool HAS_PHI, bool WRITE = true>
+__device__ __forceinline__ void stream_cell(const Grid &g, const float *__restrict__ f,
+                                            const uint8_t *__restrict__ fl, const float *__restrict__ phi,
+                                            const Inflow &in, float *rho_b, float *vel_b, int y, int x,
+                                            float out[9])
+{
+    const uint8_t me = fl[cell(g, y, y, x)];
+    if (me == CT_OUTFLOW)
+    {
+        const int sy = y == 0 ? y + 1 : (y == g.H - 1 ? y - 1 : y);
+        const int sx = x == 0 ? x + 1 : (x == g.W - 1 ? x - 1 : x);
+        if (sy != y || sx != x)
+        {
+            stream_with_inflow<HAS_PHI, false>(g, f, fl, phi, in, rho_b, vel_b, sy, sx, out);
+            return;
+        }
+    }
+    stream_with_inflow<HAS_PHI, WRITE>(g, f, fl, phi, in, rho_b, vel_b, y, x, out);
+}
+
+// ------------------------------------------------------------------------------------------
+// R2 / R7: moments (LBM_macro_compute_2d.py:316-351, 273-295).  Sequential fp32 sums, q = 0..8.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float sum9(const float f[9])
+{
+    float s = f[0];
+#pragma unroll
+    for (int q = 1; q < 9; ++q)
+        s = s + f[q];
+    return s;
+}
+
+__device__ __forceinline__ void momentum9(const float f[9], float &mx, float &my)
+{
+    // sum_q f_q e_q accumulated in direction order; terms with e = 0 add +-0 and are skipped
+    mx = ((((f[1] - f[3]) + f[5]) - f[6]) - f[7]) + f[8];
+    my = ((((f[2] - f[4]) + f[5]) + f[6]) - f[7]) - f[8];
+}
+
+// ------------------------------------------------------------------------------------------
+// R3: equilibrium (LBM_collision_2d.py:236-263).  Host-prepared fp32 scalars in EqParams.
+// ------------------------------------------------------------------------------------------
+struct EqParams
+{
+    float c;        // (float)(dx/dt)
+    float inv_cs2;  // (float)(1/cs2): torch divides by a python scalar as a reciprocal multiply
+};
+
+__device__ __forceinline__ void half_force_shift(float rho, float &ux, float &uy, float fx, float fy)
+{
+    // LBM_collision_2d.py:246-250: u += where(rho <= 1e-10, 0, 0.5 * force / rho)
+    const float ax = rho <= 1e-10f ? 0.f : (0.5f * fx) / rho;
+    const float ay = rho <= 1e-10f ? 0.f : (0.5f * fy) / rho;
+    ux = ux + ax;
+    uy = uy + ay;
+}
+
+__device__ __forceinline__ void equilibrium(const EqParams &p, float rho, float ux, float uy, float feq[9])
+{
+    const float uv = ux * ux + uy * uy;
+    const float huv = (0.5f * uv) * p.inv_cs2;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+    {
+        const float eu = (ux * (float)JRL_EX(q)) * p.c + (uy * (float)JRL_EY(q)) * p.c;
+        const float rw = rho * weight(q);
+        const float a = rw * (1.f + eu * p.inv_cs2);
+        const float b = rw * ((((0.5f * eu) * eu) * p.inv_cs2) * p.inv_cs2 - huv);
+        feq[q] = a + b;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// R4 / R4m / R4k: collision operators.
+// ------------------------------------------------------------------------------------------
+struct CollideParams
+{
+    EqParams eq;
+    int op;          // OP_BGK / OP_MRT / OP_KBC
+    int kbc_type;    // KBCType code (OP_KBC only)
+    int convection;  // BGK only: advection-diffusion form, per-direction relaxation
+    int axisym;
+    float omega;     // (float)(1/tau)   (tau_D when convection)
+    float dt;        // (float)dt
+    float conv_k1;   // (float)(dt * (1 - 0.5/tau_D))      LBM_collision_2d.py:516-521
+    float conv_k2;   // (float)(1 - 0.5/tau_D)             LBM_collision_2d.py:375-384
+    float beta;      // (float)(1/(2 tau))                 LBM_collision_KBC_2d.py:237
+    float inv_beta;  // (float)(1/beta)
+    float two_m_inv_beta;  // (float)(2 - 1/beta)
+    float mrt[81];   // M^-1 S M, row-major (LBM_collision_MRT_2d.py:59-69), built on the host
+};
+
+// Entropic KBC relaxation, LBM_collision_KBC_2d.py:70-249.  Returns Omega in om[].
+__device__ __forceinline__ void kbc_omega(const CollideParams &p, float rho, float ux, float uy,
+                                          const float f[9], const float feq[9], float om[9])
+{
+    const int type = p.kbc_type;
+    if (type == KBC_LBGK)
+    {
+        // ds = f - feq, dh = 0, gamma = 2: Omega = -beta * (2 ds + 2 * 0)
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
+            om[q] = -p.beta * (2.f * (f[q] - feq[q]) + 2.f * 0.f);
+        return;
+    }
+    const bool central = (type == KBC_A || type == KBC_B);
+    // second-order moments M20, M11, M02 of f and feq
+    float m20 = 0.f, m11 = 0.f, m02 = 0.f, q20 = 0.f, q11 = 0.f, q02 = 0.f;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+    {
+        float a20, a11, a02;
+        if (central)
+        {
+            const float dxm = (float)JRL_EX(q) - ux;  // (c e - u), c = 1 (:96-105)
+            const float dym = (float)JRL_EY(q) - uy;
+            a20 = (dxm * dxm) * 1.f;
+            a11 = dxm * dym;
+            a02 = 1.f * (dym * dym);
+        }
+        else
+        {
+            a20 = (float)(JRL_EX(q) * JRL_EX(q));
+            a11 = (float)(JRL_EX(q) * JRL_EY(q));
+            a02 = (float)(JRL_EY(q) * JRL_EY(q));
+        }
+        m20 = m20 + a20 * f[q];
+        m11 = m11 + a11 * f[q];
+        m02 = m02 + a02 * f[q];
+        q20 = q20 + a20 * feq[q];
+        q11 = q11 + a11 * feq[q];
+        q02 = q02 + a02 * feq[q];
+    }
+    const float T = m20 + m02, N = m20 - m02, P = m11;
+    const float Te = q20 + q02, Ne = q20 - q02, Pe = q11;
+    float s[9], se[9];
+    if (type == KBC_A || type == KBC_C)
+    {
+        s[0] = rho - T;
+        s[1] = 0.5f * (0.5f * (T + N) + rho * ux);
+        s[2] = 0.5f * (0.5f * (T - N) + rho * uy);
+        s[3] = 0.5f * (0.5f * (T + N) - rho * ux);
+        s[4] = 0.5f * (0.5f * (T - N) - rho * uy);
+        se[0] = rho - Te;
+        se[1] = 0.5f * (0.5f * (Te + Ne) + rho * ux);
+        se[2] = 0.5f * (0.5f * (Te - Ne) + rho * uy);
+        se[3] = 0.5f * (0.5f * (Te + Ne) - rho * ux);
+        se[4] = 0.5f * (0.5f * (Te - Ne) - rho * uy);
+    }
+    else
+    {
+        s[0] = rho + 0.f * N;
+        s[1] = 0.5f * (0.5f * N + rho * ux);
+        s[2] = 0.5f * (0.5f * (-N) + rho * uy);
+        s[3] = 0.5f * (0.5f * N - rho * ux);
+        s[4] = 0.5f * (0.5f * (-N) - rho * uy);
+        se[0] = rho + 0.f * Ne;
+        se[1] = 0.5f * (0.5f * Ne + rho * ux);
+        se[2] = 0.5f * (0.5f * (-Ne) + rho * uy);
+        se[3] = 0.5f * (0.5f * Ne - rho * ux);
+        se[4] = 0.5f * (0.5f * (-Ne) - rho * uy);
+    }
+    s[5] = 0.25f * P;
+    s[6] = 0.25f * (-P);
+    s[7] = 0.25f * P;
+    s[8] = 0.25f * (-P);
+    se[5] = 0.25f * Pe;
+    se[6] = 0.25f * (-Pe);
+    se[7] = 0.25f * Pe;
+    se[8] = 0.25f * (-Pe);
+    const float eps = 1e-10f;
+    float ds[9], dh[9];
+    float dsdh = 0.f, dhdh = 0.f;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+    {
+        ds[q] = s[q] - se[q];
+        dh[q] = (f[q] - feq[q]) - ds[q];
+        const float den = feq[q] + eps;
+        const float a = (ds[q] * dh[q]) / den;
+        const float b = (dh[q] * dh[q]) / den;
+        dsdh = q == 0 ? a : dsdh + a;
+        dhdh = q == 0 ? b : dhdh + b;
+    }
+    const float gamma = p.inv_beta - p.two_m_inv_beta * (dsdh / (dhdh + eps));
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        om[q] = -p.beta * (2.f * ds[q] + gamma * dh[q]);
+}
+
+// Per-cell collision of a non-obstacle cell given its moments.  `r` is mesh_grid x (radius) of
+// the cell, used by the axisymmetric concentration form only.  `G` (nullable) is the fluid
+// axisymmetric source already evaluated for this cell (LBM_collision_2d.py:386-427).
+//   BGK        LBM_collision_2d.py:473-555
+//   MRT        LBM_collision_MRT_2d.py:84-102, 121-184
+//   KBC        LBM_collision_KBC_2d.py:251-317
+//   OP   : OP_BGK / OP_MRT / OP_KBC, or -1 to dispatch on p.op at run time
+//   CONV : 0 = momentum form; 1 = advection-diffusion with x-axis symmetry; 2 = advection-
+//          diffusion with y-axis symmetry (r = r'); 3 = advection-diffusion, no symmetry
+template <int OP, int CONV>
+__device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, float ux, float uy,
+                                             bool has_force, float fx, float fy, float r,
+                                             const float *G, float f[9])
+{
+    const int op = OP < 0 ? p.op : OP;
+    if (has_force)
+        half_force_shift(rho, ux, uy, fx, fy);
+    float feq[9];
+    equilibrium(p.eq, rho, ux, uy, feq);
+    if (op == OP_BGK)
+    {
+        if (CONV == 1)
+        {
+            // omega_q = 1/tau_D + dt(1 - 0.5/tau_D) e_qx / r ; G_q = -(u_r/r) heq_q (1 - 0.5/tau_D - 0.5 s_q)
+            const float ur_r = (-ux) / r;
+#pragma unroll
+            for (int q = 0; q < 9; ++q)
+            {
+                const float er = (float)JRL_EX(q);
+                const float w = p.omega + (p.conv_k1 * er) / r;
+                const float s = (p.conv_k2 * er) / r;
+                const float g = (ur_r * feq[q]) * (p.conv_k2 - 0.5f * s);
+                f[q] = (f[q] + w * (feq[q] - f[q])) + p.dt * g;
+            }
+        }
+        else if (CONV == 2)
+        {
+            // LBM_collision_2d.py:428-436: G = w_q * A1, A1 = -rho u_z / r', uniform omega
+            // (the per-direction branch for the y axis is unreachable, :522).  r here is r'.
+            const float a1 = ((-rho) * uy) / r;
+#pragma unroll
+            for (int q = 0; q < 9; ++q)
+                f[q] = (f[q] + p.omega * (feq[q] - f[q])) + p.dt * (a1 * weight(q));
+        }
+        else
+        {
+#pragma unroll
+            for (int q = 0; q < 9; ++q)
+                f[q] = (f[q] + p.omega * (feq[q] - f[q])) + (G ? p.dt * G[q] : 0.f);
+        }
+        return;
+    }
+    float om[9];
+    if (op == OP_MRT)
+    {
+        float d[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
+            d[q] = feq[q] - f[q];
+#pragma unroll
+        for (int i = 0; i < 9; ++i)
+        {
+            float acc = 0.f;
+#pragma unroll
+            for (int j = 0; j < 9; ++j)
+#if JRL_MRT_FMA
+                acc = fmaf(p.mrt[i * 9 + j], d[j], acc);
+#else
+                acc = acc + p.mrt[i * 9 + j] * d[j];
+#endif
+            om[i] = acc;
+        }
+    }
+    else
+        kbc_omega(p, rho, ux, uy, f, feq, om);
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        f[q] = (f[q] + om[q]) + (G ? p.dt * G[q] : 0.f);
+}
+
+}  // namespace jrl

@@ -1,0 +1,711 @@
+// Per-operator kernels of libjrl_lbm.so: one launch per reference solver-object method
+// (streaming, moments, equilibrium, stencils, collision, moving wall, strip reductions).
+// They exist for API parity -- each replaces one pybind call or one chain of 10-100 torch
+// ops -- and as the building blocks the fused step (fused.cu) is checked against bit for bit.
+// One thread per cell; blockIdx.y = batch element.
+#include "common.cuh"
+#include "stencil.cuh"
+
+namespace jrl {
+
+#define JRL_CELL_PROLOGUE                                                       \
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;       \
+    if (i >= g.HW)                                                              \
+        return;                                                                 \
+    const long long b = blockIdx.y;                                             \
+    const int y = (int)(i / g.W);                                               \
+    const int x = (int)(i - (long long)y * g.W);                                \
+    (void)x;                                                                    \
+    (void)y;
+
+// ---- R1 ------------------------------------------------------------------------------------
+template <bool HAS_PHI>
+__global__ void __launch_bounds__(kThreads) k_stream(Grid g, const uint8_t *__restrict__ flags,
+                                                     const float *__restrict__ f, const float *__restrict__ phi,
+                                                     float *__restrict__ f_new, Inflow in)
+{
+    JRL_CELL_PROLOGUE
+    float out[9];
+    stream_cell<HAS_PHI>(g, f + b * 9 * g.HW, flags + b * g.HW, HAS_PHI ? phi + b * g.HW : nullptr, in,
+                         in.rho ? in.rho + b * g.HW : nullptr, in.vel ? in.vel + b * 2 * g.HW : nullptr, y, x, out);
+    float *o = f_new + b * 9 * g.HW + i;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        o[q * g.HW] = out[q];
+}
+
+__global__ void __launch_bounds__(kThreads) k_rebounce(Grid g, const float *__restrict__ f,
+                                                       const uint8_t *__restrict__ flags, float *__restrict__ f_new)
+{
+    JRL_CELL_PROLOGUE
+    const bool obs = flags[b * g.HW + i] == CT_OBSTACLE;
+    const float *s = f + b * 9 * g.HW + i;
+    float *o = f_new + b * 9 * g.HW + i;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        o[q * g.HW] = s[(obs ? opp(q) : q) * g.HW];
+}
+
+// ---- R2 / R7 ---------------------------------------------------------------------------------
+// mode 0: LBMMacroCompute2d.macro_compute (torch-op path); mode 1: kernel_macompute_2d_forward
+template <int MODE>
+__global__ void __launch_bounds__(kThreads) k_moments(Grid g, const float *__restrict__ f,
+                                                      const float *__restrict__ rho_old,
+                                                      const float *__restrict__ vel_old,
+                                                      const uint8_t *__restrict__ flags, float *__restrict__ rho_new,
+                                                      float *__restrict__ vel_new, int use_contact, float c)
+{
+    JRL_CELL_PROLOGUE
+    const float *s = f + b * 9 * g.HW + i;
+    float fc[9];
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        fc[q] = s[q * g.HW];
+    const bool obs = flags[b * g.HW + i] == CT_OBSTACLE;
+    float r, vx, vy;
+    if (obs)
+    {
+        r = rho_old[b * g.HW + i];
+        vx = vel_old[b * 2 * g.HW + i];
+        vy = vel_old[b * 2 * g.HW + g.HW + i];
+        // contact_angle_correctness zeroes obstacle cells off the outer ring; ring cells are
+        // finished by k_contact_ring
+        if (MODE == 0 && use_contact && x != 0 && y != 0 && x != g.W - 1 && y != g.H - 1)
+            r = 0.f;
+    }
+    else if (MODE == 0)
+    {
+        r = sum9(fc);
+        float mx, my;
+        momentum9(fc, mx, my);
+        const float inv = c / r;
+        vx = mx * inv;
+        vy = my * inv;
+    }
+    else
+    {
+        r = 0.f + fc[0];
+#pragma unroll
+        for (int q = 1; q < 9; ++q)
+            r = r + fc[q];
+        float mx = 0.f, my = 0.f;
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
+        {
+            mx = mx + (fc[q] * (float)JRL_EX(q)) * c;
+            my = my + (fc[q] * (float)JRL_EY(q)) * c;
+        }
+        vx = mx / r;
+        vy = my / r;
+    }
+    rho_new[b * g.HW + i] = r;
+    vel_new[b * 2 * g.HW + i] = vx;
+    vel_new[b * 2 * g.HW + g.HW + i] = vy;
+}
+
+// contact_angle_correctness on the outer ring, LBM_macro_compute_2d.py:237-271.  One thread per
+// ring cell.  `pre(cell)` is the density before the correction: rho_old at OBSTACLE cells (the
+// caller guarantees rho_new does not alias it), the freshly summed rho_new elsewhere.
+__global__ void k_contact_ring(Grid g, const float *__restrict__ rho_old, const uint8_t *__restrict__ flags,
+                               float *__restrict__ rho_new, float tn)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ring = 2 * (g.H + g.W) - 4;
+    if (t >= ring)
+        return;
+    const long long b = blockIdx.y;
+    const uint8_t *fl = flags + b * g.HW;
+    const float *ro = rho_old + b * g.HW;
+    float *rn = rho_new + b * g.HW;
+    int y, x;
+    if (t < g.W) { y = 0; x = t; }
+    else if (t < 2 * g.W) { y = g.H - 1; x = t - g.W; }
+    else if (t < 2 * g.W + g.H - 2) { y = t - 2 * g.W + 1; x = 0; }
+    else { y = t - (2 * g.W + g.H - 2) + 1; x = g.W - 1; }
+    if (fl[(long long)y * g.W + x] != CT_OBSTACLE)
+        return;
+    auto pre = [&](int yy, int xx) -> float {
+        const long long k = (long long)yy * g.W + xx;
+        return fl[k] == CT_OBSTACLE ? ro[k] : rn[k];
+    };
+    const int H = g.H, W = g.W;
+    auto left = [&](int yy) { return pre(yy, 2) + tn * fabsf(pre(yy + 1, 1) - pre(yy - 1, 1)); };
+    auto right = [&](int yy) { return pre(yy, W - 3) + tn * fabsf(pre(yy + 1, W - 2) - pre(yy - 1, W - 2)); };
+    auto bottom = [&](int xx) { return pre(2, xx) + tn * fabsf(pre(1, xx + 1) - pre(1, xx - 1)); };
+    auto top = [&](int xx) { return pre(H - 3, xx) + tn * fabsf(pre(H - 2, xx + 1) - pre(H - 2, xx - 1)); };
+    float v;
+    const bool cy0 = y == 0, cy1 = y == H - 1, cx0 = x == 0, cx1 = x == W - 1;
+    if (cy0 && cx0)
+        v = 0.5f * (left(1) + bottom(1));
+    else if (cy1 && cx0)
+        v = 0.5f * (left(H - 2) + top(1));
+    else if (cy0 && cx1)
+        v = 0.5f * (bottom(W - 2) + right(1));
+    else if (cy1 && cx1)
+        v = 0.5f * (0.f + 0.f);  // sic: the reference averages two interior (zero) cells (:269)
+    else if (cx0)
+        v = left(y);
+    else if (cx1)
+        v = right(y);
+    else if (cy0)
+        v = bottom(x);
+    else
+        v = top(x);
+    rn[(long long)y * g.W + x] = v;
+}
+
+// mode 0: macro_compute_C (torch path, optional clamp); mode 1: kernel_macompute_C_2d_forward
+template <int MODE>
+__global__ void __launch_bounds__(kThreads) k_moments_C(Grid g, const float *__restrict__ h,
+                                                        const float *__restrict__ C_old,
+                                                        const uint8_t *__restrict__ flags, float *__restrict__ C_new,
+                                                        int clamp01, const float *__restrict__ vel,
+                                                        const float *__restrict__ mesh, double half_dt)
+{
+    JRL_CELL_PROLOGUE
+    float v;
+    if (flags[b * g.HW + i] == CT_OBSTACLE)
+        v = C_old[b * g.HW + i];
+    else
+    {
+        const float *s = h + b * 9 * g.HW + i;
+        float fc[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
+            fc[q] = s[q * g.HW];
+        if (MODE == 0)
+            v = sum9(fc);
+        else
+        {
+            v = 0.f + fc[0];
+#pragma unroll
+            for (int q = 1; q < 9; ++q)
+                v = v + fc[q];
+            if (g.axisym == AXI_X)
+            {
+                const double den = 1.0 + (half_dt * (double)vel[b * 2 * g.HW + i]) / (double)mesh[b * 2 * g.HW + i];
+                v = (float)((double)v / den);
+            }
+        }
+    }
+    if (MODE == 0 && clamp01)
+        v = fminf(fmaxf(v, 0.f), 1.f);
+    C_new[b * g.HW + i] = v;
+}
+
+// ---- R3 ----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_feq(Grid g, const float *__restrict__ rho, const float *__restrict__ vel,
+                                                  const float *__restrict__ force, float *__restrict__ feq, EqParams p)
+{
+    JRL_CELL_PROLOGUE
+    const float r = rho[b * g.HW + i];
+    float ux = vel[b * 2 * g.HW + i], uy = vel[b * 2 * g.HW + g.HW + i];
+    if (force)
+        half_force_shift(r, ux, uy, force[b * 2 * g.HW + i], force[b * 2 * g.HW + g.HW + i]);
+    float e[9];
+    equilibrium(p, r, ux, uy, e);
+    float *o = feq + b * 9 * g.HW + i;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        o[q * g.HW] = e[q];
+}
+
+// ---- R6 stencil ops ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_grad(Grid g, const float *__restrict__ s, const uint8_t *__restrict__ flags,
+                                                   float *__restrict__ grad, double twelve_dx)
+{
+    JRL_CELL_PROLOGUE
+    const uint8_t *fl = flags + b * g.HW;
+    const float *sb = s + b * g.HW;
+    float gx = 0.f, gy = 0.f;
+    if (fl[i] != CT_OBSTACLE)
+    {
+        const Stencil st = make_stencil(g, fl, y, x);
+        float v[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
+            v[q] = sb[st.at[q]];
+        grad_sums(st, v, gx, gy);
+        gx = div12(gx, twelve_dx);
+        gy = div12(gy, twelve_dx);
+    }
+    grad[b * 2 * g.HW + i] = gx;
+    grad[b * 2 * g.HW + g.HW + i] = gy;
+}
+
+__global__ void __launch_bounds__(kThreads) k_div(Grid g, const float *__restrict__ v2, const uint8_t *__restrict__ flags,
+                                                  float *__restrict__ dv, double twelve_dx)
+{
+    JRL_CELL_PROLOGUE
+    const uint8_t *fl = flags + b * g.HW;
+    float d = 0.f;
+    if (fl[i] != CT_OBSTACLE)
+    {
+        const Stencil st = make_stencil(g, fl, y, x);
+        float a[9], c[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
+        {
+            a[q] = v2[b * 2 * g.HW + st.at[q]];
+            c[q] = v2[b * 2 * g.HW + g.HW + st.at[q]];
+        }
+        d = div12(div_sum(a, c), twelve_dx);
+    }
+    dv[b * g.HW + i] = d;
+}
+
+// ---- R4 / R4m / R4k / R6: collision ------------------------------------------------------------
+// SRC: 0 = no stencil source; 1 = fluid axisymmetric source (3x3 stencil of rho / vel).
+template <int CONV, int SRC>
+__global__ void __launch_bounds__(kThreads) k_collide(Grid g, const __grid_constant__ CollideParams p,
+                                                      const __grid_constant__ SourceParams sp,
+                                                      const float *__restrict__ f, const float *__restrict__ rho,
+                                                      const float *__restrict__ vel, const uint8_t *__restrict__ flags,
+                                                      const float *__restrict__ force, const float *__restrict__ mesh,
+                                                      float *__restrict__ f_out)
+{
+    JRL_CELL_PROLOGUE
+    const float *s = f + b * 9 * g.HW + i;
+    float *o = f_out + b * 9 * g.HW + i;
+    float fc[9];
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        fc[q] = s[q * g.HW];
+    if (flags[b * g.HW + i] != CT_OBSTACLE)
+    {
+        const float r0 = rho[b * g.HW + i];
+        const float ux = vel[b * 2 * g.HW + i], uy = vel[b * 2 * g.HW + g.HW + i];
+        float fx = 0.f, fy = 0.f;
+        if (force)
+        {
+            fx = force[b * 2 * g.HW + i];
+            fy = force[b * 2 * g.HW + g.HW + i];
+        }
+        float r = 1.f;
+        if (CONV == 1)
+            r = mesh[b * 2 * g.HW + i];
+        else if (CONV == 2)
+            r = y == 0 ? 1.f : mesh[b * 2 * g.HW + g.HW + i] - sp.half_dx;
+        float G[9];
+        if (SRC)
+            axisym_fluid_source(sp, g, flags + b * g.HW, rho + b * g.HW, vel + b * 2 * g.HW, mesh + b * 2 * g.HW, y, x, G);
+        collide_cell<-1, CONV>(p, r0, ux, uy, force != nullptr, fx, fy, r, SRC ? G : nullptr, fc);
+    }
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        o[q * g.HW] = fc[q];
+}
+
+// ---- R5 --------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_wall(Grid g, WallParams p, const float *__restrict__ vel,
+                                                   const uint8_t *__restrict__ flags, const float *__restrict__ f,
+                                                   float *__restrict__ f_new, const float *__restrict__ phi,
+                                                   const float *__restrict__ obs_vel)
+{
+    JRL_CELL_PROLOGUE
+    const float *s = f + b * 9 * g.HW + i;
+    float *o = f_new + b * 9 * g.HW + i;
+    float fc[9];
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        fc[q] = s[q * g.HW];
+    wall_cell(p, g, flags + b * g.HW, vel + b * 2 * g.HW, phi + b * g.HW, obs_vel ? obs_vel + b * 2 * g.HW : nullptr, y, x, fc);
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+        o[q * g.HW] = fc[q];
+}
+
+#ifndef JRL_HOST_EMU  // warp-shuffle kernels: GPU only
+// ---- R8: strip reductions, one warp, shuffle tree --------------------------------------------------
+__global__ void k_strip_flux(const float *__restrict__ C, const float *__restrict__ mesh, int y0, int ncol, int W,
+                             float *__restrict__ out2)
+{
+    const int k = threadIdx.x;
+    float flux = 0.f, plain = 0.f;
+    for (int c = k; c < ncol; c += 32)
+    {
+        // area_k = pi (k+1)^2 - pi k^2 in fp32 (demo_2d_LBM_JRL_C_cylinder.py:176-180)
+        const float pi = 3.14159274101257324f;
+        const float area = pi * (float)((c + 1) * (c + 1)) - pi * (float)(c * c);
+        const float c0 = C[(long long)y0 * W + c], c1 = C[(long long)y0 * W + c + 1];
+        const float dz = c0 - C[(long long)(y0 - 1) * W + c];
+        const float r0 = mesh[(long long)y0 * W + c], r1 = mesh[(long long)y0 * W + c + 1];
+        const float dr = (r1 * c1 - r0 * c0) / r0;
+        flux += (dz + dr) * area;
+        plain += c0 * area;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+    {
+        flux += __shfl_xor_sync(0xffffffffu, flux, off);
+        plain += __shfl_xor_sync(0xffffffffu, plain, off);
+    }
+    if (k == 0)
+    {
+        out2[0] = flux;
+        out2[1] = plain;
+    }
+}
+
+// ---- R9 (extension): momentum exchange over halfway bounce-back links -------------------------------
+__global__ void __launch_bounds__(kThreads) k_momentum_exchange(Grid g, const float *__restrict__ f,
+                                                                const uint8_t *__restrict__ flags, double *out2)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long b = blockIdx.y;
+    double fx = 0.0, fy = 0.0;
+    if (i < g.HW)
+    {
+        const uint8_t *fl = flags + b * g.HW;
+        const int y = (int)(i / g.W), x = (int)(i - (long long)y * g.W);
+        if (fl[i] != CT_OBSTACLE)
+        {
+#pragma unroll
+            for (int q = 1; q < 9; ++q)
+            {
+                const int xx = x + JRL_EX(q), yy = y + JRL_EY(q);
+                if (xx < 0 || yy < 0 || xx >= g.W || yy >= g.H)
+                    continue;
+                if (fl[(long long)yy * g.W + xx] == CT_OBSTACLE)
+                {
+                    const double v = 2.0 * (double)f[b * 9 * g.HW + q * g.HW + i];
+                    fx += JRL_EX(q) * v;
+                    fy += JRL_EY(q) * v;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+    {
+        fx += __shfl_xor_sync(0xffffffffu, fx, off);
+        fy += __shfl_xor_sync(0xffffffffu, fy, off);
+    }
+    __shared__ double sx[kThreads / 32], sy[kThreads / 32];
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0)
+    {
+        sx[w] = fx;
+        sy[w] = fy;
+    }
+    __syncthreads();
+    if (w == 0)
+    {
+        fx = l < kThreads / 32 ? sx[l] : 0.0;
+        fy = l < kThreads / 32 ? sy[l] : 0.0;
+#pragma unroll
+        for (int off = 4; off > 0; off >>= 1)
+        {
+            fx += __shfl_xor_sync(0xffffffffu, fx, off);
+            fy += __shfl_xor_sync(0xffffffffu, fy, off);
+        }
+        if (l == 0 && (fx != 0.0 || fy != 0.0))
+        {
+            atomicAdd(out2, fx);
+            atomicAdd(out2 + 1, fy);
+        }
+    }
+}
+
+#endif  // !JRL_HOST_EMU
+
+// ---- halo staging ----------------------------------------------------------------------------------
+__global__ void k_halo_copy(float *__restrict__ dst, const float *__restrict__ src, int C, long long plane_dst,
+                            long long plane_src, long long off_dst, long long off_src, long long n)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const int c = blockIdx.y;
+    (void)C;
+    dst[c * plane_dst + off_dst + i] = src[c * plane_src + off_src + i];
+}
+
+}  // namespace jrl
+
+// ====================================================================================================
+// C ABI launchers
+// ====================================================================================================
+using namespace jrl;
+
+namespace {
+
+inline dim3 cell_grid(const Grid &g, int B) { return dim3(blocks_for(g.HW), (unsigned)B, 1); }
+
+}  // namespace
+
+namespace jrl {
+
+EqParams make_eq(double dx, double dt)
+{
+    const double c = dx / dt;
+    const double cs2 = c * c / 3.0;
+    EqParams p;
+    p.c = (float)c;
+    p.inv_cs2 = (float)(1.0 / cs2);
+    return p;
+}
+
+void make_collide(CollideParams &p, SourceParams &sp, int op, int kbc_type, int is_convection, int axisym,
+                  double dx, double dt, double tau, const float *mrt_host)
+{
+    const double c = dx / dt;
+    const double cs2 = c * c / 3.0;
+    p.eq = make_eq(dx, dt);
+    p.op = op;
+    p.kbc_type = kbc_type;
+    p.convection = is_convection;
+    p.axisym = axisym;
+    p.omega = (float)(1.0 / tau);
+    p.dt = (float)dt;
+    p.conv_k1 = (float)(dt * (1.0 - 0.5 / tau));
+    p.conv_k2 = (float)(1.0 - 0.5 / tau);
+    const double beta = 1.0 / (2.0 * tau);
+    p.beta = (float)beta;
+    p.inv_beta = (float)(1.0 / beta);
+    p.two_m_inv_beta = (float)(2.0 - 1.0 / beta);
+    for (int k = 0; k < 81; ++k)
+        p.mrt[k] = mrt_host ? mrt_host[k] : 0.f;
+    sp.axisym = axisym;
+    sp.visc = (float)(cs2 * (tau - 0.5));
+    sp.cs2 = (float)cs2;
+    sp.inv_cs2 = (float)(1.0 / cs2);
+    sp.dt = (float)dt;
+    sp.half_dx = (float)(0.5 * dx);
+    sp.k3 = (float)(dt * (tau - 1.0) * cs2);
+    sp.twelve_dx = 12.0 * dx;
+}
+
+WallParams make_wall(double dt, double dx, double tau)
+{
+    WallParams p;
+    p.c = (float)(dx / dt);
+    p.cs2 = (float)((double)(p.c * p.c) / 3.0);
+    p.tau = tau;
+    return p;
+}
+
+}  // namespace jrl
+
+extern "C" {
+
+int jrl_stream_f32(const uint8_t *flags, const float *f, const float *phi_obs, float *f_new, float *rho, float *vel,
+                   const float *inflow_vel, double inflow_density, int axisym, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_stream_f32";
+    JRL_REQUIRE(flags && f && f_new, fn, "flags, f and f_new are required");
+    JRL_REQUIRE(f != f_new, fn, "f_new must not alias f");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "B >= 1, H >= 2, W >= 2 required");
+    JRL_REQUIRE(axisym >= 0 && axisym <= 2, fn, "axisym must be 0, 1 or 2");
+    const Grid g = make_grid(H, W, axisym);
+    Inflow in;
+    in.rho = rho;
+    in.vel = vel;
+    in.inflow_vel = inflow_vel;
+    in.has_density = inflow_density >= 0.0;
+    in.density = (float)inflow_density;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (phi_obs)
+        JRL_LAUNCH(k_stream<true>, cell_grid(g, B), kThreads, s, g, flags, f, phi_obs, f_new, in);
+    else
+        JRL_LAUNCH(k_stream<false>, cell_grid(g, B), kThreads, s, g, flags, f, nullptr, f_new, in);
+    return check_launch(fn);
+}
+
+int jrl_rebounce_f32(const float *f, const uint8_t *flags, float *f_new, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_rebounce_f32";
+    JRL_REQUIRE(flags && f && f_new && f != f_new, fn, "f, flags, f_new required; f_new must not alias f");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, 0);
+    JRL_LAUNCH(k_rebounce, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, f, flags, f_new);
+    return check_launch(fn);
+}
+
+int jrl_moments_f32(const float *f, const float *rho_old, const float *vel_old, const uint8_t *flags, float *rho_new,
+                    float *vel_new, int use_contact, float contact_tan, double c, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_moments_f32";
+    JRL_REQUIRE(f && rho_old && vel_old && flags && rho_new && vel_new, fn, "null pointer");
+    JRL_REQUIRE(rho_new != rho_old && vel_new != vel_old, fn, "outputs must not alias the previous-step moments");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    JRL_REQUIRE(!use_contact || (H >= 4 && W >= 4), fn, "contact-angle wall density needs H, W >= 4");
+    const Grid g = make_grid(H, W, 0);
+    cudaStream_t s = (cudaStream_t)stream;
+    JRL_LAUNCH(k_moments<0>, cell_grid(g, B), kThreads, s, g, f, rho_old, vel_old, flags, rho_new, vel_new, use_contact, (float)c);
+    if (use_contact)
+    {
+        const int ring = 2 * (H + W) - 4;
+        JRL_LAUNCH(k_contact_ring, dim3(blocks_for(ring, 128), B), 128, s, g, rho_old, flags, rho_new, contact_tan);
+    }
+    return check_launch(fn);
+}
+
+int jrl_moments_kernel_f32(const float *f, const float *rho_old, const float *vel_old, const uint8_t *flags,
+                           float *rho_new, float *vel_new, double c, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_moments_kernel_f32";
+    JRL_REQUIRE(f && rho_old && vel_old && flags && rho_new && vel_new, fn, "null pointer");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, 0);
+    JRL_LAUNCH(k_moments<1>, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, f, rho_old, vel_old, flags, rho_new, vel_new, 0, (float)c);
+    return check_launch(fn);
+}
+
+int jrl_moments_C_f32(const float *h, const float *C_old, const uint8_t *flags, float *C_new, int clamp01, int B, int H,
+                      int W, void *stream)
+{
+    const char *fn = "jrl_moments_C_f32";
+    JRL_REQUIRE(h && C_old && flags && C_new, fn, "null pointer");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, 0);
+    JRL_LAUNCH(k_moments_C<0>, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, h, C_old, flags, C_new, clamp01, nullptr, nullptr, 0.0);
+    return check_launch(fn);
+}
+
+int jrl_moments_C_kernel_f32(double dt, const float *h, const float *C_old, const uint8_t *flags, const float *vel,
+                             const float *mesh_grid, float *C_new, int axisym, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_moments_C_kernel_f32";
+    JRL_REQUIRE(h && C_old && flags && C_new, fn, "null pointer");
+    JRL_REQUIRE(axisym != JRL_AXI_X || (vel && mesh_grid), fn, "x-axis symmetry needs vel and mesh_grid");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, axisym);
+    JRL_LAUNCH(k_moments_C<1>, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, h, C_old, flags, C_new, 0, vel, mesh_grid, 0.5 * dt);
+    return check_launch(fn);
+}
+
+int jrl_feq_f32(const float *rho, const float *vel, const float *force, float *feq, double dx, double dt, int B, int H,
+                int W, void *stream)
+{
+    const char *fn = "jrl_feq_f32";
+    JRL_REQUIRE(rho && vel && feq, fn, "null pointer");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, 0);
+    JRL_LAUNCH(k_feq, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, rho, vel, force, feq, make_eq(dx, dt));
+    return check_launch(fn);
+}
+
+int jrl_grad_f32(const float *s, const uint8_t *flags, float *grad, double dx, int axisym, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_grad_f32";
+    JRL_REQUIRE(s && flags && grad, fn, "null pointer");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, axisym);
+    JRL_LAUNCH(k_grad, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, s, flags, grad, 12.0 * dx);
+    return check_launch(fn);
+}
+
+int jrl_div_f32(const float *v, const uint8_t *flags, float *div, double dx, int axisym, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_div_f32";
+    JRL_REQUIRE(v && flags && div, fn, "null pointer");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, axisym);
+    JRL_LAUNCH(k_div, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, v, flags, div, 12.0 * dx);
+    return check_launch(fn);
+}
+
+int jrl_collide_f32(const jrl_collide_desc *d, void *stream)
+{
+    const char *fn = "jrl_collide_f32";
+    JRL_REQUIRE(d, fn, "null descriptor");
+    JRL_REQUIRE(d->f && d->rho && d->vel && d->flags && d->f_out, fn, "f, rho, vel, flags, f_out required");
+    JRL_REQUIRE(dims_ok(d->B, d->H, d->W), fn, "bad dimensions");
+    JRL_REQUIRE(d->op >= 0 && d->op <= 2, fn, "unknown operator");
+    JRL_REQUIRE(d->op != JRL_OP_MRT || d->mrt, fn, "MRT needs the 9x9 matrix");
+    JRL_REQUIRE(!(d->is_convection && d->op != JRL_OP_BGK), fn, "convection is BGK only (LBM_collision_MRT_2d.py:138)");
+    JRL_REQUIRE(d->op != JRL_OP_KBC || d->kbc_type == JRL_KBC_LBGK || d->kbc_type == JRL_KBC_A || d->kbc_type == JRL_KBC_B ||
+                    d->kbc_type == JRL_KBC_C || d->kbc_type == JRL_KBC_D,
+                fn, "Please specific a right KBC Type value");
+    JRL_REQUIRE(d->axisym == 0 || d->mesh_grid, fn, "axisymmetric collision needs mesh_grid");
+    const bool stencil_src = d->axisym != 0 && !d->is_convection;
+    const Grid g = make_grid(d->H, d->W, d->axisym);
+    CollideParams p;
+    SourceParams sp;
+    make_collide(p, sp, d->op, d->kbc_type, d->is_convection, d->axisym, d->dx, d->dt, d->tau, d->mrt);
+    cudaStream_t s = (cudaStream_t)stream;
+    const dim3 grid = cell_grid(g, d->B);
+#define JRL_LAUNCH_COLLIDE(CONV, SRC)                                                                         \
+    do                                                                                                        \
+    {                                                                                                         \
+        auto kern = k_collide<CONV, SRC>;                                                                     \
+        JRL_LAUNCH(kern, grid, kThreads, s, g, p, sp, d->f, d->rho, d->vel, d->flags, d->force, d->mesh_grid, \
+                   d->f_out);                                                                                 \
+    } while (0)
+    if (d->is_convection)
+    {
+        if (d->axisym == JRL_AXI_X)
+            JRL_LAUNCH_COLLIDE(1, 0);
+        else if (d->axisym == JRL_AXI_Y)
+            JRL_LAUNCH_COLLIDE(2, 0);
+        else
+            JRL_LAUNCH_COLLIDE(3, 0);
+    }
+    else if (stencil_src)
+        JRL_LAUNCH_COLLIDE(0, 1);
+    else
+        JRL_LAUNCH_COLLIDE(0, 0);
+#undef JRL_LAUNCH_COLLIDE
+    return check_launch(fn);
+}
+
+int jrl_wall_f32(double dt, double dx, double tau, const float *vel, const uint8_t *flags, const float *f, float *f_new,
+                 const float *phi_obs, const float *obs_vel, int axisym, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_wall_f32";
+    JRL_REQUIRE(vel && flags && f && f_new && phi_obs, fn, "vel, flags, f, f_new, phi_obs required");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, axisym);
+    JRL_LAUNCH(k_wall, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, make_wall(dt, dx, tau), vel, flags, f, f_new, phi_obs, obs_vel);
+    return check_launch(fn);
+}
+
+int jrl_strip_flux_f32(const float *C, const float *mesh_grid, int y0, int ncol, float *out2, int H, int W, void *stream)
+{
+    const char *fn = "jrl_strip_flux_f32";
+    JRL_REQUIRE(C && mesh_grid && out2, fn, "null pointer");
+    JRL_REQUIRE(y0 >= 1 && y0 < H && ncol >= 1 && ncol + 1 <= W, fn, "strip outside the grid");
+#ifdef JRL_HOST_EMU
+    return fail_arg(fn, "warp-shuffle kernel: not part of the host emulation build");
+#else
+    JRL_LAUNCH(k_strip_flux, 1, 32, (cudaStream_t)stream, C, mesh_grid, y0, ncol, W, out2);
+    return check_launch(fn);
+#endif
+}
+
+int jrl_momentum_exchange_f32(const float *f_post, const uint8_t *flags, double *out2, int B, int H, int W, void *stream)
+{
+    const char *fn = "jrl_momentum_exchange_f32";
+    JRL_REQUIRE(f_post && flags && out2, fn, "null pointer");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+#ifdef JRL_HOST_EMU
+    return fail_arg(fn, "warp-shuffle kernel: not part of the host emulation build");
+#else
+    const Grid g = make_grid(H, W, 0);
+    JRL_LAUNCH(k_momentum_exchange, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, f_post, flags, out2);
+    return check_launch(fn);
+#endif
+}
+
+int jrl_halo_pack_f32(const float *field, float *staging, int C, int Hloc, int W, int row, int nrows, void *stream)
+{
+    const char *fn = "jrl_halo_pack_f32";
+    JRL_REQUIRE(field && staging && C > 0 && nrows > 0 && row >= 0 && row + nrows <= Hloc, fn, "bad arguments");
+    const long long n = (long long)nrows * W;
+    JRL_LAUNCH(k_halo_copy, dim3(blocks_for(n), C), kThreads, (cudaStream_t)stream, staging, field, C, n, (long long)Hloc * W, 0,
+                                                                               (long long)row * W, n);
+    return check_launch(fn);
+}
+
+int jrl_halo_unpack_f32(float *field, const float *staging, int C, int Hloc, int W, int row, int nrows, void *stream)
+{
+    const char *fn = "jrl_halo_unpack_f32";
+    JRL_REQUIRE(field && staging && C > 0 && nrows > 0 && row >= 0 && row + nrows <= Hloc, fn, "bad arguments");
+    const long long n = (long long)nrows * W;
+    JRL_LAUNCH(k_halo_copy, dim3(blocks_for(n), C), kThreads, (cudaStream_t)stream, field, staging, C, (long long)Hloc * W, n,
+                                                                               (long long)row * W, 0, n);
+    return check_launch(fn);
+}
+
+}  // extern "C"
