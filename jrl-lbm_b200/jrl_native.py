@@ -1,0 +1,162 @@
+"""ctypes binding of libjrl_lbm.so (include/jrl_lbm.h) -- the only way this package computes.
+
+There is NO CPU fallback: `load()` opens the nvcc-built library that sits next to this file
+and raises if it is missing, and every wrapper rejects tensors that are not CUDA / contiguous
+/ fp32 (uint8 for flags).  PyTorch is used for device memory and streams only; pointers are
+`tensor.data_ptr()` and the stream is `torch.cuda.current_stream()`.
+
+(The CPU test-suite exercises the same kernel SOURCES compiled for the host by
+tests/host_emu/build.sh; it installs that library through `_install_test_library`, which is
+never called by product code.)
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_double, c_float, c_int, c_void_p
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libjrl_lbm.so")
+
+_lib = None
+_allow_cpu_tensors = False  # flipped only by _install_test_library (tests/host_emu)
+
+AXI_NOT, AXI_X, AXI_Y = 0, 1, 2
+OP_BGK, OP_MRT, OP_KBC = 0, 1, 2
+
+
+class CollideDesc(Structure):  # struct jrl_collide_desc
+    _fields_ = [("B", c_int), ("H", c_int), ("W", c_int), ("axisym", c_int), ("op", c_int), ("kbc_type", c_int),
+                ("is_convection", c_int), ("dx", c_double), ("dt", c_double), ("tau", c_double),
+                ("mrt", c_void_p), ("f", c_void_p), ("rho", c_void_p), ("vel", c_void_p), ("flags", c_void_p),
+                ("force", c_void_p), ("mesh_grid", c_void_p), ("f_out", c_void_p)]
+
+
+class StepDesc(Structure):  # struct jrl_step_desc
+    _fields_ = [("B", c_int), ("H", c_int), ("W", c_int), ("axisym", c_int), ("op", c_int), ("kbc_type", c_int),
+                ("is_convection", c_int), ("use_contact", c_int), ("contact_tan", c_float), ("clamp01", c_int),
+                ("dx", c_double), ("dt", c_double), ("tau", c_double), ("mrt", c_void_p), ("flags", c_void_p),
+                ("f_in", c_void_p), ("f_out", c_void_p), ("phi_obs", c_void_p), ("rho", c_void_p),
+                ("vel", c_void_p), ("rho_out", c_void_p), ("vel_out", c_void_p), ("force", c_void_p),
+                ("mesh_grid", c_void_p), ("inflow_vel", c_void_p), ("inflow_density", c_double),
+                ("use_wall", c_int), ("obs_vel", c_void_p), ("slab_row0", c_int), ("slab_rows", c_int),
+                ("row_begin", c_int), ("row_end", c_int), ("force_vec", c_int)]
+
+
+_vp, _i, _d, _f = c_void_p, c_int, c_double, c_float
+# name -> argtypes; every symbol include/jrl_lbm.h declares (tests/test_abi.py checks the list against the header)
+PROTOTYPES = {
+    "jrl_version": [],
+    "jrl_last_error": [],
+    "jrl_stream_f32": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _i, _i, _i, _i, _vp],
+    "jrl_rebounce_f32": [_vp, _vp, _vp, _i, _i, _i, _vp],
+    "jrl_moments_f32": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _d, _i, _i, _i, _vp],
+    "jrl_moments_kernel_f32": [_vp, _vp, _vp, _vp, _vp, _vp, _d, _i, _i, _i, _vp],
+    "jrl_moments_C_f32": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "jrl_moments_C_kernel_f32": [_d, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "jrl_feq_f32": [_vp, _vp, _vp, _vp, _d, _d, _i, _i, _i, _vp],
+    "jrl_grad_f32": [_vp, _vp, _vp, _d, _i, _i, _i, _i, _vp],
+    "jrl_div_f32": [_vp, _vp, _vp, _d, _i, _i, _i, _i, _vp],
+    "jrl_collide_f32": [POINTER(CollideDesc), _vp],
+    "jrl_wall_f32": [_d, _d, _d, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "jrl_strip_flux_f32": [_vp, _vp, _i, _i, _vp, _i, _i, _vp],
+    "jrl_momentum_exchange_f32": [_vp, _vp, _vp, _i, _i, _i, _vp],
+    "jrl_step_f32": [POINTER(StepDesc), _vp],
+    "jrl_halo_pack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "jrl_halo_unpack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
+}
+
+
+def _bind(lib):
+    for name, argtypes in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the library lacks a declared symbol
+        fn.argtypes = argtypes
+        fn.restype = c_char_p if name == "jrl_last_error" else c_int
+    return lib
+
+
+def load():
+    """Open libjrl_lbm.so (built by `make -C jrl-lbm_b200` / __graft_entry__.build()).  Fails loudly."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build the sm_100a library first (make -C jrl-lbm_b200). "
+                "This package has no CPU or PyTorch fallback.")
+        _lib = _bind(ctypes.CDLL(LIB_PATH))
+    return _lib
+
+
+def _install_test_library(path):
+    """TESTS ONLY: route calls to the host-compiled build of the same kernel sources
+    (tests/host_emu/libjrl_lbm_emu.so) and accept CPU tensors.  Pass None to undo."""
+    global _lib, _allow_cpu_tensors
+    if path is None:
+        _lib, _allow_cpu_tensors = None, False
+    else:
+        _lib, _allow_cpu_tensors = _bind(ctypes.CDLL(path)), True
+
+
+def stream_ptr(like: torch.Tensor):
+    if like.is_cuda:
+        return c_void_p(torch.cuda.current_stream(like.device).cuda_stream)
+    return None
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        msg = load().jrl_last_error()
+        raise RuntimeError(f"libjrl_lbm {what}: {msg.decode() if msg else rc}")
+
+
+def tensor_ptr(t, name, dtype=torch.float32, shape=None, like=None, optional=False):
+    """Validated raw device pointer of `t` (the reference checks nothing and
+    reinterprets memory on a wrong dtype; the drop-in raises instead)."""
+    if t is None or (isinstance(t, torch.Tensor) and t.numel() == 0 and optional):
+        if optional:
+            return None
+        raise RuntimeError(f"{name}: tensor required")
+    if not isinstance(t, torch.Tensor):
+        raise RuntimeError(f"{name}: expected a torch.Tensor, got {type(t).__name__}")
+    if t.dtype != dtype:
+        raise RuntimeError(f"{name}: dtype {t.dtype} not supported, expected {dtype} (fp32 path only)")
+    if not t.is_cuda and not _allow_cpu_tensors:
+        raise RuntimeError(f"{name}: tensor is on {t.device}; JRL-LBM-B200 has no CPU path (CUDA tensors only)")
+    if like is not None and t.device != like.device:
+        raise RuntimeError(f"{name}: device {t.device} differs from {like.device}")
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name}: tensor must be contiguous [B,C,H,W]")
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise RuntimeError(f"{name}: shape {tuple(t.shape)}, expected {tuple(shape)}")
+    return c_void_p(t.data_ptr())
+
+
+class device_of:
+    """Context manager: make `t`'s device current so the launch lands on it (multi-GPU processes)."""
+
+    def __init__(self, t):
+        self.ctx = torch.cuda.device(t.device) if t.is_cuda else None
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *a):
+        if self.ctx is not None:
+            self.ctx.__exit__(*a)
+
+
+# count of library launches issued through this module (bench.py's gpu_launches claim)
+launch_count = 0
+
+
+def call(name, *args, like):
+    """Invoke one library entry point on `like`'s device and current stream."""
+    global launch_count
+    lib = load()
+    with device_of(like):
+        rc = getattr(lib, name)(*args, stream_ptr(like))
+    launch_count += 1
+    check(rc, name)

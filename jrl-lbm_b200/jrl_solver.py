@@ -1,0 +1,405 @@
+"""Host-side mirror of the reference's solver objects (`src/LBM`), backed by libjrl_lbm.so.
+
+Same class names, method names, keyword names, return arity and in-place side effects as the
+reference (every method cites the reference method it replaces, paths
+relative to the reference tree), so demo/*.py and batch_validation.py drive it unchanged.
+Each method is ONE library launch (the reference: one custom kernel plus 10-80 torch
+elementwise launches and one or two full copies of f).  The fused single-launch step and the
+multi-GPU row-slab driver live in jrl_step.py / jrl_slab.py.
+
+No CPU path: CUDA fp32 tensors only (uint8 flags); anything else raises RuntimeError.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+
+import torch
+
+import jrl_native as N
+
+CELL_OBSTACLE = 2
+CELL_INFLOW_2 = 32
+_KBC_CODES = (0, 0x85, 0x86, 0x89, 0x8A)
+
+
+def _dims(f, name="f"):
+    if not isinstance(f, torch.Tensor) or f.dim() != 4:
+        raise RuntimeError(f"{name}: expected a [B,C,H,W] tensor")
+    B, _, H, W = f.shape
+    return int(B), int(H), int(W)
+
+
+def _full(t, shape, name, like):
+    """Broadcast `t` (e.g. a [1,2,1,1] gravity term times a scalar) to the full contiguous shape."""
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor):
+        t = torch.as_tensor(t, dtype=like.dtype, device=like.device)
+    if tuple(t.shape) != tuple(shape):
+        t = t.expand(shape)
+    return t.contiguous()
+
+
+# --------------------------------------------------------------------------------------------------
+# Streaming                                      (LBM_propagation/LBM_propagation_2d.py:95-186)
+# --------------------------------------------------------------------------------------------------
+class LBMPropagation2d:
+    rank = 2
+    type_flags = ["x", "X", "y", "Y", "z", "Z"]
+
+    def __init__(self, tau, axisymmetric_type=0, device=torch.device("cpu"), dtype=torch.float32):
+        self._tau = tau
+        self.axisymmetric_type = int(axisymmetric_type)
+        self.device = device
+        self.dtype = dtype
+        self._inflow2_cache = None  # (data_ptr, _version, shape) -> bool
+
+    def _has_inflow2(self, flags):
+        # LBM_propagation_2d.py:58 syncs the host every step with `(flags == INFLOW_2).any()`;
+        # the answer only changes when `flags` is written, which bumps the tensor's version counter.
+        key = (flags.data_ptr(), flags._version, tuple(flags.shape))
+        if self._inflow2_cache is None or self._inflow2_cache[0] != key:
+            self._inflow2_cache = (key, bool((flags == CELL_INFLOW_2).any()))
+        return self._inflow2_cache[1]
+
+    def propagation(self, f, flags, phi_obs=None, rho=None, vel=None, inflow_vel=None, inflow_density=None,
+                    is_convection=False):
+        """Pull streaming with every link rule; one launch of jrl_stream_f32.
+        Returns f_new, or (rho, vel, f_new) under the reference's rule (LBM_propagation_2d.py:52-59,
+        89-92); rho / vel are mutated in place at INFLOW / INFLOW_2 cells (propagation.cu:300-362)."""
+        B, H, W = _dims(f)
+        inflow_info = inflow_density is not None or inflow_vel is not None
+        if inflow_info:
+            assert rho is not None
+        p_flags = N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f)
+        if not inflow_info:
+            inflow_info = self._has_inflow2(flags)
+        p_f = N.tensor_ptr(f, "f", shape=(B, 9, H, W))
+        p_phi = N.tensor_ptr(phi_obs, "phi_obs", shape=(B, 1, H, W), like=f, optional=True)
+        p_rho = N.tensor_ptr(rho, "rho", shape=(B, 1, H, W), like=f, optional=True)
+        p_vel = N.tensor_ptr(vel, "vel", shape=(B, 2, H, W), like=f, optional=True)
+        p_iv = N.tensor_ptr(inflow_vel, "inflow_vel", shape=(2,), like=f, optional=True)
+        f_new = torch.empty_like(f)
+        N.call("jrl_stream_f32", p_flags, p_f, p_phi, ctypes.c_void_p(f_new.data_ptr()), p_rho, p_vel, p_iv,
+               -1.0 if inflow_density is None else float(inflow_density), self.axisymmetric_type, B, H, W, like=f)
+        if inflow_info:
+            return (torch.Tensor([]) if rho is None else rho, torch.Tensor([]) if vel is None else vel, f_new)
+        return f_new
+
+    def rebounce_obstacle(self, f, flags):
+        """OBSTACLE cells get their populations reversed (LBM_propagation_2d.py:181-186)."""
+        B, H, W = _dims(f)
+        f_new = torch.empty_like(f)
+        N.call("jrl_rebounce_f32", N.tensor_ptr(f, "f", shape=(B, 9, H, W)),
+               N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f),
+               ctypes.c_void_p(f_new.data_ptr()), B, H, W, like=f)
+        return f_new
+
+
+# --------------------------------------------------------------------------------------------------
+# Moments                                        (LBM_macro_compute/LBM_macro_compute_2d.py:105-361)
+# --------------------------------------------------------------------------------------------------
+class LBMMacroCompute2d:
+    rank = 2
+    type_flags = ["x", "X", "y", "Y", "z", "Z"]
+
+    def __init__(self, Q=9, tau=1.0, density_liquid=0.265, density_gas=0.038, rho_liquid=0.265, rho_gas=0.038,
+                 axisymmetric_type=0, contact_angle=0.5 * math.pi, device=torch.device("cpu"), dtype=torch.float32):
+        if Q != 9:
+            raise RuntimeError("D2Q9 only")
+        self._Q = Q
+        self._tau = tau
+        self._density_liquid = density_liquid
+        self._density_gas = density_gas
+        self._rho_liquid = rho_liquid
+        self._rho_gas = rho_gas
+        self.axisymmetric_type = int(axisymmetric_type)
+        self._contact_angle = contact_angle
+        self.device = device
+        self.dtype = dtype
+        self._contact_tan_cache = None
+
+    def _contact_tan(self):
+        """tan(pi/2 - contact_angle) as the reference evaluates it (LBM_macro_compute_2d.py:246):
+        fp32 tensor arithmetic for a tensor angle.  Evaluated once (one host read), not per step."""
+        ca = self._contact_angle
+        key = id(ca)
+        if self._contact_tan_cache is None or self._contact_tan_cache[0] != key:
+            if isinstance(ca, torch.Tensor):
+                t = torch.tan(math.pi / 2.0 - ca.detach().to("cpu", torch.float32).reshape(-1)[0])
+                val = float(t)
+            else:
+                val = math.tan(math.pi / 2.0 - float(ca))
+            self._contact_tan_cache = (key, val)
+        return self._contact_tan_cache[1]
+
+    def macro_compute(self, dx, dt, f, rho, vel, flags, g=None, pressure=None, density=None):
+        """rho = sum f, u = sum f e c / rho; OBSTACLE cells keep the old values, with the
+        contact-angle wall density when contact_angle is not None (LBM_macro_compute_2d.py:316-351,
+        237-271).  One launch of jrl_moments_f32 (+ a ring kernel for the wall density)."""
+        B, H, W = _dims(f)
+        rho_new = torch.empty((B, 1, H, W), dtype=f.dtype, device=f.device)
+        vel_new = torch.empty((B, 2, H, W), dtype=f.dtype, device=f.device)
+        use_contact = self._contact_angle is not None
+        N.call("jrl_moments_f32", N.tensor_ptr(f, "f", shape=(B, 9, H, W)),
+               N.tensor_ptr(rho, "rho", shape=(B, 1, H, W), like=f), N.tensor_ptr(vel, "vel", shape=(B, 2, H, W), like=f),
+               N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f),
+               ctypes.c_void_p(rho_new.data_ptr()), ctypes.c_void_p(vel_new.data_ptr()),
+               int(use_contact), self._contact_tan() if use_contact else 0.0, float(dx) / float(dt), B, H, W, like=f)
+        if density is not None:
+            # multiphase density remap (LBM_macro_compute_2d.py:338-349); no demo takes this branch
+            density = self._density_gas + (self._density_liquid - self._density_gas) * (
+                (rho_new - self._rho_gas) / (self._rho_liquid - self._rho_gas))
+            return [rho_new, vel_new, density]
+        return [rho_new, vel_new]
+
+    def macro_compute_C(self, dx, dt, h, C, flags, vel, mesh_grid):
+        """C = sum h; OBSTACLE cells keep C (LBM_macro_compute_2d.py:273-295)."""
+        B, H, W = _dims(h, "h")
+        C_new = torch.empty((B, 1, H, W), dtype=h.dtype, device=h.device)
+        N.call("jrl_moments_C_f32", N.tensor_ptr(h, "h", shape=(B, 9, H, W)),
+               N.tensor_ptr(C, "C", shape=(B, 1, H, W), like=h),
+               N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=h),
+               ctypes.c_void_p(C_new.data_ptr()), 0, B, H, W, like=h)
+        return C_new
+
+    def ApplyCompute_C(self, dx, dt, h, C, flags, vel, mesh_grid):
+        """The reference's CUDA twin with the axisymmetric division (macro_compute.cu:22-78)."""
+        B, H, W = _dims(h, "h")
+        C_new = torch.empty((B, 1, H, W), dtype=h.dtype, device=h.device)
+        N.call("jrl_moments_C_kernel_f32", float(dt), N.tensor_ptr(h, "h", shape=(B, 9, H, W)),
+               N.tensor_ptr(C, "C", shape=(B, 1, H, W), like=h),
+               N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=h),
+               N.tensor_ptr(vel, "vel", shape=(B, 2, H, W), like=h, optional=True),
+               N.tensor_ptr(mesh_grid, "mesh_grid", shape=(B, 2, H, W), like=h, optional=True),
+               ctypes.c_void_p(C_new.data_ptr()), self.axisymmetric_type, B, H, W, like=h)
+        return C_new
+
+    def ApplyCompute_fluid(self, dx, dt, f, rho, vel, flags, g=None, pressure=None, density=None):
+        """Moments without the wall-density step (macro_compute.cu:80-157)."""
+        B, H, W = _dims(f)
+        rho_new = torch.empty((B, 1, H, W), dtype=f.dtype, device=f.device)
+        vel_new = torch.empty((B, 2, H, W), dtype=f.dtype, device=f.device)
+        N.call("jrl_moments_kernel_f32", N.tensor_ptr(f, "f", shape=(B, 9, H, W)),
+               N.tensor_ptr(rho, "rho", shape=(B, 1, H, W), like=f), N.tensor_ptr(vel, "vel", shape=(B, 2, H, W), like=f),
+               N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f),
+               ctypes.c_void_p(rho_new.data_ptr()), ctypes.c_void_p(vel_new.data_ptr()),
+               float(dx) / float(dt), B, H, W, like=f)
+        return [rho_new, vel_new]
+
+    def get_vort(self, vel, dx):
+        """Central-difference vorticity for the PNG dumps (LBM_macro_compute_2d.py:353-361); runs
+        every 10-1000 steps, off the per-step path, so it stays a handful of torch ops."""
+        v = ((vel[..., 0:1, 2:, 1:-1] - vel[..., 0:1, :-2, 1:-1])
+             - (vel[..., 1:2, 1:-1, 2:] - vel[..., 1:2, 1:-1, :-2])) / (2.0 * dx)
+        return torch.nn.functional.pad(v, pad=(1, 1, 1, 1), mode="replicate")
+
+
+# --------------------------------------------------------------------------------------------------
+# Collision                      (LBM_collision/LBM_collision_2d.py, _MRT_2d.py, _KBC_2d.py)
+# --------------------------------------------------------------------------------------------------
+_MRT_M = [
+    [1, 1, 1, 1, 1, 1, 1, 1, 1],
+    [-4, -1, -1, -1, -1, 2, 2, 2, 2],
+    [4, -2, -2, -2, -2, 1, 1, 1, 1],
+    [0, 1, 0, -1, 0, 1, -1, -1, 1],
+    [0, -2, 0, 2, 0, 1, -1, -1, 1],
+    [0, 0, 1, 0, -1, 1, 1, -1, -1],
+    [0, 0, -2, 0, 2, 1, 1, -1, -1],
+    [0, 1, -1, 1, -1, 0, 0, 0, 0],
+    [0, 0, 0, 0, 0, 1, -1, 1, -1],
+]  # Lallemand-Luo moment basis in this lattice's direction order, LBM_collision_MRT_2d.py:41-57
+
+
+def mrt_operator(tau):
+    """M^-1 S M as a host fp32 [9,9] tensor, S = diag(0, s7, s7, 0, s4, 0, s4, s7, s7), s7 = 1/tau,
+    s4 = 8(2 - s7)/(8 - s7)  (LBM_collision_MRT_2d.py:59-69).  Built once per preset_KBC."""
+    M = torch.tensor(_MRT_M, dtype=torch.float32)
+    s7 = 1.0 / tau
+    s4 = 8.0 * (2 - s7) / (8 - s7)
+    S = torch.tensor([0.0, s7, s7, 0.0, s4, 0.0, s4, s7, s7], dtype=torch.float32).reshape(9, 1)
+    return (torch.linalg.inv(M) @ (S * M)).contiguous()
+
+
+class LBMCollision2d:
+    """BGK (and the advection-diffusion form used for the concentration field)."""
+    rank = 2
+    type_flags = ["x", "X", "y", "Y", "z", "Z"]
+    _op = N.OP_BGK
+
+    def __init__(self, Q=9, tau=1.0, density_liquid=0.265, density_gas=0.038, rho_liquid=0.265, rho_gas=0.038,
+                 gravity_strength=0.0, kappa=0.08, tau_f=0.7, tau_g=0.7, axisymmetric_type=0,
+                 contact_angle=math.pi / 2.0, device=torch.device("cpu"), dtype=torch.float32):
+        if Q != 9:
+            raise RuntimeError("D2Q9 only")
+        self._Q = Q
+        self._tau = tau
+        self._density_liquid = density_liquid
+        self._density_gas = density_gas
+        self._rho_liquid = rho_liquid
+        self._rho_gas = rho_gas
+        self._kappa = kappa
+        self._tau_f = tau_f
+        self._tau_g = tau_g
+        self.axisymmetric_type = int(axisymmetric_type)
+        self._contact_angle = contact_angle
+        self.device = device
+        self.dtype = dtype
+        # LBM_collision_2d.py:166-171; demos form `force = density * collision._gravity`
+        self._gravity = torch.tensor([0.0, -gravity_strength], dtype=dtype).reshape(1, 2, 1, 1).to(device)
+        self._mrt = None
+
+    # -- configuration ---------------------------------------------------------------------------
+    def preset_KBC(self, dx, dt, tau, tau_D=None):
+        """LBM_collision_2d.py:212-215."""
+        self._tau = tau
+        if tau_D is not None:
+            self._tau_D = tau_D
+
+    # -- single-launch operators -------------------------------------------------------------------
+    def get_feq_(self, dx, dt, rho, vel, tau=None, force=None, is_convection=False):
+        """Second-order equilibrium with the half-force velocity shift (LBM_collision_2d.py:236-286)."""
+        B, H, W = _dims(vel, "vel")
+        rho = _full(rho, (B, 1, H, W), "rho", vel)
+        force = _full(force, (B, 2, H, W), "force", vel)
+        feq = torch.empty((B, 9, H, W), dtype=vel.dtype, device=vel.device)
+        N.call("jrl_feq_f32", N.tensor_ptr(rho, "rho", shape=(B, 1, H, W), like=vel),
+               N.tensor_ptr(vel, "vel", shape=(B, 2, H, W)),
+               N.tensor_ptr(force, "force", shape=(B, 2, H, W), like=vel, optional=True),
+               ctypes.c_void_p(feq.data_ptr()), float(dx), float(dt), B, H, W, like=vel)
+        return feq
+
+    def get_grad(self, rho, dx, flags):
+        """9-point isotropic gradient, collision_2d.cu:22-148 via LBM_collision_2d.py:308-309."""
+        B, H, W = _dims(rho, "rho")
+        rho = rho.contiguous()
+        out = torch.empty((B, 2, H, W), dtype=rho.dtype, device=rho.device)
+        N.call("jrl_grad_f32", N.tensor_ptr(rho, "rho", shape=(B, 1, H, W)),
+               N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=rho),
+               ctypes.c_void_p(out.data_ptr()), float(dx), self.axisymmetric_type, B, H, W, like=rho)
+        return out
+
+    def get_div(self, vel, dx, flags):
+        """9-point isotropic divergence, collision_2d.cu:150-220 via LBM_collision_2d.py:311-312."""
+        B, H, W = _dims(vel, "vel")
+        vel = vel.contiguous()
+        out = torch.empty((B, 1, H, W), dtype=vel.dtype, device=vel.device)
+        N.call("jrl_div_f32", N.tensor_ptr(vel, "vel", shape=(B, 2, H, W)),
+               N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=vel),
+               ctypes.c_void_p(out.data_ptr()), float(dx), self.axisymmetric_type, B, H, W, like=vel)
+        return out
+
+    def _operator(self, is_convection, KBC_type):
+        return self._op, 0, (self._tau_D if is_convection else self._tau)
+
+    def collision(self, dx, dt, f, rho, vel, flags, force=None, mesh_grid=None, is_convection=False, KBC_type=None,
+                  **unused):
+        """f' = f + Omega(f, feq) + dt G; OBSTACLE cells keep f.  One launch of jrl_collide_f32
+        replaces LBMCollision2d.collision (LBM_collision_2d.py:473-555) including get_feq_ and the
+        axisymmetric source (:343-471) with its gradient / divergence stencils."""
+        B, H, W = _dims(f)
+        op, kbc, tau = self._operator(is_convection, KBC_type)
+        force = _full(force, (B, 2, H, W), "force", f)
+        d = N.CollideDesc()
+        d.B, d.H, d.W = B, H, W
+        d.axisym = self.axisymmetric_type
+        d.op, d.kbc_type, d.is_convection = op, kbc, int(bool(is_convection))
+        d.dx, d.dt, d.tau = float(dx), float(dt), float(tau)
+        d.mrt = self._mrt.data_ptr() if (op == N.OP_MRT and self._mrt is not None) else None
+        d.f = N.tensor_ptr(f, "f", shape=(B, 9, H, W))
+        d.rho = N.tensor_ptr(rho, "rho", shape=(B, 1, H, W), like=f)
+        d.vel = N.tensor_ptr(vel, "vel", shape=(B, 2, H, W), like=f)
+        d.flags = N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f)
+        d.force = N.tensor_ptr(force, "force", shape=(B, 2, H, W), like=f, optional=True)
+        d.mesh_grid = N.tensor_ptr(mesh_grid, "mesh_grid", shape=(B, 2, H, W), like=f, optional=True)
+        f_out = torch.empty_like(f)
+        d.f_out = f_out.data_ptr()
+        N.call("jrl_collide_f32", ctypes.byref(d), like=f)
+        return f_out
+
+
+class LBMCollisionMRT2d(LBMCollision2d):
+    """Multiple-relaxation-time operator (LBM_collision_MRT_2d.py:11-184); what demo_2d_LBM_KBC.py
+    and demo_2d_LBM_cylinder.py really run (their KBC_type argument is ignored)."""
+    _op = N.OP_MRT
+
+    def preset_KBC(self, dx, dt, tau, tau_D=None):
+        self._tau = tau
+        self._mrt = mrt_operator(tau)
+        self.Minv_S_M = self._mrt.reshape(1, 1, 1, 9, 9).to(self.device)
+        if tau_D is not None:
+            self._tau_D = tau_D
+
+    def _operator(self, is_convection, KBC_type):
+        assert not is_convection  # LBM_collision_MRT_2d.py:138
+        if self._mrt is None:
+            raise AttributeError("LBMCollisionMRT2d: call preset_KBC(dx, dt, tau) first")  # reference: no Minv_S_M yet
+        return N.OP_MRT, 0, self._tau
+
+
+class LBMCollisionKBC2d(LBMCollision2d):
+    """Entropic KBC stabiliser (LBM_collision_KBC_2d.py:11-317)."""
+    _op = N.OP_KBC
+
+    def _operator(self, is_convection, KBC_type):
+        assert not is_convection
+        code = 0 if KBC_type is None else int(KBC_type)
+        if code not in _KBC_CODES:
+            raise RuntimeError("Please specific a right KBC Type value")  # LBM_collision_KBC_2d.py:235
+        return N.OP_KBC, code, self._tau
+
+
+# --------------------------------------------------------------------------------------------------
+# Moving-wall coupling            (LBM_solid_fluid_coupling/LBM_boundary_2d.py:76-158)
+# --------------------------------------------------------------------------------------------------
+class LBMBoundary2d:
+    rank = 2
+    type_flags = ["x", "X", "y", "Y", "z", "Z"]
+
+    def __init__(self, tau, axisymmetric_type=0, device=torch.device("cpu"), dtype=torch.float32):
+        self._tau = tau
+        self.axisymmetric_type = int(axisymmetric_type)
+        self.device = device
+        self.dtype = dtype
+
+    def solve_boundary(self, dt, dx, rho, vel, flags, f, phi_obs, obs_vel, tau=None, is_convection=False):
+        """Regularised moving-wall reconstruction at fluid cells next to obstacles; one launch of
+        jrl_wall_f32 (solid_fluid_coupling.cu:25-252).  `rho` and `is_convection` are unused by the
+        reference kernel too."""
+        B, H, W = _dims(f)
+        tau = self._tau if tau is None else tau
+        f_new = torch.empty_like(f)
+        N.call("jrl_wall_f32", float(dt), float(dx), float(tau), N.tensor_ptr(vel, "vel", shape=(B, 2, H, W), like=f),
+               N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f),
+               N.tensor_ptr(f, "f", shape=(B, 9, H, W)), ctypes.c_void_p(f_new.data_ptr()),
+               N.tensor_ptr(phi_obs, "phi_obs", shape=(B, 1, H, W), like=f),
+               N.tensor_ptr(obs_vel, "obs_vel", shape=(B, 2, H, W), like=f, optional=True),
+               self.axisymmetric_type, B, H, W, like=f)
+        return f_new
+
+
+# --------------------------------------------------------------------------------------------------
+# R8 / R9 reductions (new entry points; the demos do these with ~20 tiny torch launches per step)
+# --------------------------------------------------------------------------------------------------
+def strip_flux(C, mesh_grid, y0, ncol, out=None):
+    """[flux, plain] of demo_2d_LBM_JRL_C_cylinder.py:344-362 / 45degree.py:353-376 for row y0 on
+    the device (one warp); returns a device [2] tensor (no host sync)."""
+    B, H, W = _dims(C, "C")
+    if out is None:
+        out = torch.empty(2, dtype=C.dtype, device=C.device)
+    N.call("jrl_strip_flux_f32", N.tensor_ptr(C, "C", shape=(B, 1, H, W)),
+           N.tensor_ptr(mesh_grid, "mesh_grid", shape=(B, 2, H, W), like=C), int(y0), int(ncol),
+           ctypes.c_void_p(out.data_ptr()), H, W, like=C)
+    return out
+
+
+def momentum_exchange(f_post, flags):
+    """Extension (absent from the reference): momentum-exchange force on all OBSTACLE
+    cells, device [2] float64 (Fx, Fy)."""
+    B, H, W = _dims(f_post)
+    out = torch.zeros(2, dtype=torch.float64, device=f_post.device)
+    N.call("jrl_momentum_exchange_f32", N.tensor_ptr(f_post, "f", shape=(B, 9, H, W)),
+           N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f_post),
+           ctypes.c_void_p(out.data_ptr()), B, H, W, like=f_post)
+    return out

@@ -19,7 +19,6 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 sys.path.insert(0, HERE)
-sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200"))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
@@ -37,7 +36,12 @@ def main():
     import torch
     import ref_cpu
     ref_cpu.import_reference()
-    import jrl_scenarios as S
+    # jrl-lbm_b200/ must NOT be on sys.path here: its `src` package (the drop-in) would shadow
+    # the reference's `src` namespace package.  Load the scenario builders by file path.
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("jrl_scenarios", os.path.join(ROOT, "jrl-lbm_b200", "jrl_scenarios.py"))
+    S = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(S)
     from golden_cases import CASES
     ref_api = S.api_from_src()
     if args.check:
