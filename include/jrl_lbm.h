@@ -162,7 +162,7 @@ typedef struct jrl_step_desc
     const float *mesh_grid;
     const float *inflow_vel;
     double inflow_density;  /* < 0: none */
-    /* moving wall (R5) between streaming and moments; needs phi_obs and the previous-step vel */
+    /* moving wall (R5) between streaming and moments; needs phi_obs or wall_phi, and the previous-step vel */
     int use_wall;
     const float *obs_vel;
     /* Multi-GPU row slab.  slab_rows == 0: every plane holds the whole grid [H, W].
@@ -176,6 +176,9 @@ typedef struct jrl_step_desc
        row_begin == row_end == 0: all stored rows. */
     int row_begin, row_end;
     int force_vec;          /* 0 = widest cells-per-thread the extents/alignment allow; 1, 2, 4 */
+    const float *wall_phi;  /* phi_obs seen by the moving-wall step; NULL: same as phi_obs.
+                               (demo_2d_LBM_cylinder.py:139-157 streams WITHOUT phi_obs -- plain halfway
+                               bounce-back -- but passes phi_obs to solve_boundary) */
 } jrl_step_desc;
 int jrl_step_f32(const jrl_step_desc *d, void *stream);
 

@@ -26,6 +26,7 @@ struct StepArgs
     const float *f_in;
     float *f_out;
     const float *phi;
+    const float *wall_phi;
     const float *rho;  // previous-step density / concentration (kept at OBSTACLE cells)
     const float *vel;  // previous-step velocity, or the advecting velocity when convection
     float *rho_out;
@@ -179,7 +180,7 @@ __global__ void __launch_bounds__(kThreads) k_step(const __grid_constant__ StepA
             else
                 stream_cell<false, false>(g, f, fl, nullptr, in, const_cast<float *>(rho), const_cast<float *>(vel), y, x, fc[k]);
             if (a.use_wall)
-                wall_cell(a.wp, g, fl, vel, phi, a.obs_vel ? a.obs_vel + b * 2 * g.HW : nullptr, y, x, fc[k],
+                wall_cell(a.wp, g, fl, vel, a.wall_phi + b * g.HW, a.obs_vel ? a.obs_vel + b * 2 * g.HW : nullptr, y, x, fc[k],
                           a.inflow_vel);
         }
     }
@@ -315,7 +316,7 @@ extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream)
                 "the axisymmetric FLUID source needs neighbours' post-stream moments: use the two-launch path");
     JRL_REQUIRE(!(d->is_convection && d->axisym != 0) || d->mesh_grid, fn, "axisymmetric concentration step needs mesh_grid");
     JRL_REQUIRE(!d->is_convection || d->vel, fn, "concentration step needs the advecting velocity in `vel`");
-    JRL_REQUIRE(!d->use_wall || (d->phi_obs && d->vel), fn, "moving wall needs phi_obs and the previous-step vel");
+    JRL_REQUIRE(!d->use_wall || ((d->phi_obs || d->wall_phi) && d->vel), fn, "moving wall needs phi_obs (or wall_phi) and the previous-step vel");
     JRL_REQUIRE(!d->use_wall || !d->vel_out || d->vel_out != d->vel, fn, "moving wall reads neighbours' previous vel: vel_out must not alias vel");
     JRL_REQUIRE(!d->use_contact || (d->rho && d->rho_out && d->rho_out != d->rho), fn,
                 "contact-angle wall density needs rho and a distinct rho_out");
@@ -339,6 +340,7 @@ extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream)
     a.f_in = d->f_in;
     a.f_out = d->f_out;
     a.phi = d->phi_obs;
+    a.wall_phi = d->wall_phi ? d->wall_phi : d->phi_obs;
     a.rho = d->rho;
     a.vel = d->vel;
     a.rho_out = d->rho_out;

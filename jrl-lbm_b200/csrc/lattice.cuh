@@ -492,6 +492,7 @@ __device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, 
                                              const float *G, float f[9])
 {
     const int op = OP < 0 ? p.op : OP;
+    const float ux_raw = ux, uy_raw = uy;  // the KBC moments use the unshifted velocity (LBM_collision_KBC_2d.py:295-305)
     if (has_force)
         half_force_shift(rho, ux, uy, fx, fy);
     float feq[9];
@@ -551,7 +552,7 @@ __device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, 
         }
     }
     else
-        kbc_omega(p, rho, ux, uy, f, feq, om);
+        kbc_omega(p, rho, ux_raw, uy_raw, f, feq, om);
 #pragma unroll
     for (int q = 0; q < 9; ++q)
         f[q] = (f[q] + om[q]) + (G ? p.dt * G[q] : 0.f);

@@ -42,7 +42,7 @@ class StepDesc(Structure):  # struct jrl_step_desc
                 ("vel", c_void_p), ("rho_out", c_void_p), ("vel_out", c_void_p), ("force", c_void_p),
                 ("mesh_grid", c_void_p), ("inflow_vel", c_void_p), ("inflow_density", c_double),
                 ("use_wall", c_int), ("obs_vel", c_void_p), ("slab_row0", c_int), ("slab_rows", c_int),
-                ("row_begin", c_int), ("row_end", c_int), ("force_vec", c_int)]
+                ("row_begin", c_int), ("row_end", c_int), ("force_vec", c_int), ("wall_phi", c_void_p)]
 
 
 _vp, _i, _d, _f = c_void_p, c_int, c_double, c_float

@@ -54,7 +54,7 @@ def shear_layer_state(res, device, dtype=torch.float32, rho0=0.265, Vmax=0.2, si
 
 
 def shear_layer(api, device, res=(130, 130), steps=1000, operator="bgk", kbc_type=None,
-                Re=3000.0, dx=1.0, dt=1.0, snapshots=()):
+                Re=3000.0, dx=1.0, dt=1.0, snapshots=(), fused=False):
     """operator: 'bgk' (demo_2d_LBM.py), 'mrt' (what demo_2d_LBM_KBC.py really runs)
     or 'kbc' (LBMCollisionKBC2d with `kbc_type`).  Returns final fields as numpy arrays, plus
     `snap_<n>_*` copies after each step count listed in `snapshots`."""
@@ -85,11 +85,16 @@ def shear_layer(api, device, res=(130, 130), steps=1000, operator="bgk", kbc_typ
     force = torch.zeros((1, 2, *res), dtype=dtype, device=device)
     f = collision.get_feq_(dx=dx, dt=dt, rho=density, vel=vel, force=force)
     out = {"tau": tau, "f0": _np(f)}
+    if fused:  # extension of this repo: the same loop body as ONE launch per step (jrl_step.FusedStep)
+        fs = R.create_fused_step(operator=operator, kbc_type=kbc_type if operator == "kbc" else None, dx=dx, dt=dt)
     for step in range(steps):
-        f = prop.propagation(f=f, flags=flags)
-        density, vel = macro.macro_compute(dx=dx, dt=dt, f=f, rho=density, vel=vel, flags=flags)
-        f = collision.collision(dx=dx, dt=dt, f=f, rho=density, vel=vel, flags=flags, force=force,
-                                KBC_type=kbc_type)
+        if fused:
+            f, density, vel = fs.step(f, flags, density, vel, force=force)
+        else:
+            f = prop.propagation(f=f, flags=flags)
+            density, vel = macro.macro_compute(dx=dx, dt=dt, f=f, rho=density, vel=vel, flags=flags)
+            f = collision.collision(dx=dx, dt=dt, f=f, rho=density, vel=vel, flags=flags, force=force,
+                                    KBC_type=kbc_type)
         R.step()
         if (step + 1) in snapshots:
             out[f"snap_{step + 1}_rho"] = _np(density)
@@ -111,7 +116,7 @@ def cylinder_phi(mesh_grid, center, radius):
 
 
 def cylinder(api, device, res=(800, 400), D=20, steps=2000, Re=5000.0, Vmax=0.05, dx=1.0, dt=1.0,
-             center=None, snapshots=()):
+             center=None, snapshots=(), fused=False):
     """res = [H, W]; inflow along +y from row 0, outflow at row H-1, OBSTACLE ring + cylinder,
     MRT collision with the KBC_C flag ignored, moving-wall coupling with a resting wall."""
     dtype = torch.float32
@@ -146,14 +151,20 @@ def cylinder(api, device, res=(800, 400), D=20, steps=2000, Re=5000.0, Vmax=0.05
     vel = torch.where(flags == int(CT.INFLOW), inflow_vel.reshape(-1, 2, 1, 1), vel)
     f = collision.get_feq_(dx=dx, dt=dt, rho=density, vel=vel, force=force)
     out = {"tau": tau, "flags": _np(flags), "phi_obs": _np(phi_obs)}
+    if fused:
+        fs = R.create_fused_step(operator="mrt", dx=dx, dt=dt)
     for step in range(steps):
-        density, vel, f = prop.propagation(f=f, flags=flags, rho=density, vel=vel, inflow_density=1.0,
-                                           inflow_vel=inflow_vel)
-        f = coupling.solve_boundary(dt=dt, dx=dx, rho=density, vel=vel, flags=flags, f=f, phi_obs=phi_obs,
-                                    obs_vel=phi_obs_vel, tau=tau)
-        density, vel = macro.macro_compute(dx=dx, dt=dt, f=f, rho=density, vel=vel, flags=flags)
-        f = collision.collision(dx=dx, dt=dt, f=f, rho=density, vel=vel, flags=flags, force=force,
-                                KBC_type=int(api.KBCType.KBC_C))
+        if fused:
+            f, density, vel = fs.step(f, flags, density, vel, force=force, inflow_density=1.0, inflow_vel=inflow_vel,
+                                      use_wall=True, wall_phi=phi_obs, obs_vel=phi_obs_vel)
+        else:
+            density, vel, f = prop.propagation(f=f, flags=flags, rho=density, vel=vel, inflow_density=1.0,
+                                               inflow_vel=inflow_vel)
+            f = coupling.solve_boundary(dt=dt, dx=dx, rho=density, vel=vel, flags=flags, f=f, phi_obs=phi_obs,
+                                        obs_vel=phi_obs_vel, tau=tau)
+            density, vel = macro.macro_compute(dx=dx, dt=dt, f=f, rho=density, vel=vel, flags=flags)
+            f = collision.collision(dx=dx, dt=dt, f=f, rho=density, vel=vel, flags=flags, force=force,
+                                    KBC_type=int(api.KBCType.KBC_C))
         R.step()
         if (step + 1) in snapshots:
             out[f"snap_{step + 1}_rho"] = _np(density)
@@ -267,7 +278,7 @@ def analytic_tip_velocity(mesh_grid, walks, r0):
 
 def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0.34013, radius_obs=6.50000000000001,
              inflow_height=20.50000000000001, Rg=4, vel_obs_conv=None, is_negative=True, clamp=True,
-             dx=1, dt=1, vel_field=None):
+             dx=1, dt=1, vel_field=None, fused=False):
     """Stage B.  `vel_field`: callable(mesh_grid, walks) -> normalised [1,2,H,W] velocity
     (defaults to `analytic_tip_velocity`); the demo interpolates HDF5 snapshots instead
     (:294-303).  Returns final C, h and the per-step inflow/current flux series (:344-362)."""
@@ -317,12 +328,17 @@ def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0
     C_flags[..., walks_int - 1, 0:radius_obs_int] = int(CT.INFLOW)
     C[C_flags == int(CT.OBSTACLE)] = 0.0
     balance = []
+    if fused:
+        fs = R.create_fused_step(operator="bgk", is_convection=True, tau_D=tau_D, dx=dx, dt=dt)
     for step in range(balance_steps):                                     # :215-241
         C_vel[...] = 0
-        C, _, h = prop.propagation(f=h, flags=C_flags, rho=C, vel=C_vel, is_convection=True, inflow_density=0)
-        C = macro.macro_compute_C(dx=dx, dt=dt, h=h, C=C, flags=C_flags, vel=C_vel, mesh_grid=mesh_grid)
-        h = collision_h.collision(dx=dx, dt=dt, f=h, rho=C, vel=C_vel, flags=C_flags, force=None,
-                                  mesh_grid=mesh_grid, is_convection=True, KBC_type=int(api.KBCType.KBC_C))
+        if fused:
+            h, C = fs.step(h, C_flags, C, C_vel, mesh_grid=mesh_grid, inflow_density=0)
+        else:
+            C, _, h = prop.propagation(f=h, flags=C_flags, rho=C, vel=C_vel, is_convection=True, inflow_density=0)
+            C = macro.macro_compute_C(dx=dx, dt=dt, h=h, C=C, flags=C_flags, vel=C_vel, mesh_grid=mesh_grid)
+            h = collision_h.collision(dx=dx, dt=dt, f=h, rho=C, vel=C_vel, flags=C_flags, force=None,
+                                      mesh_grid=mesh_grid, is_convection=True, KBC_type=int(api.KBCType.KBC_C))
         balance.append(((C)[..., walks_int, 0:radius_obs_int].flatten() * area).sum())
     out = {"C_balance": _np(C), "h_balance": _np(h), "tau_D": tau_D, "vel_obs_conv": vel_obs_conv}
     if vel_field is None:
@@ -340,13 +356,17 @@ def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0
         C_vel = vel_field(mesh_grid, walks) * vel_obs_conv
         C_vel[:, 0, 0:walks_int, 0:Rg_radius] = 0
         C_vel[:, 1, 0:walks_int, 0:Rg_radius] = vel_obs_conv
-        C, _, h = prop.propagation(f=h, flags=C_flags, phi_obs=phi_obs, rho=C, vel=C_vel, is_convection=True,
-                                   inflow_density=0)
-        C = macro.macro_compute_C(dx=dx, dt=dt, h=h, C=C, flags=C_flags, vel=C_vel, mesh_grid=mesh_grid)
-        if clamp:
-            C = torch.clamp(C, 0, 1)
-        h = collision_h.collision(dx=dx, dt=dt, f=h, rho=C, vel=C_vel, flags=C_flags, force=None,
-                                  mesh_grid=mesh_grid, is_convection=True, KBC_type=int(api.KBCType.KBC_C))
+        if fused:
+            h, C = fs.step(h, C_flags, C, C_vel.contiguous(), phi_obs=phi_obs, mesh_grid=mesh_grid, inflow_density=0,
+                           clamp01=clamp)
+        else:
+            C, _, h = prop.propagation(f=h, flags=C_flags, phi_obs=phi_obs, rho=C, vel=C_vel, is_convection=True,
+                                       inflow_density=0)
+            C = macro.macro_compute_C(dx=dx, dt=dt, h=h, C=C, flags=C_flags, vel=C_vel, mesh_grid=mesh_grid)
+            if clamp:
+                C = torch.clamp(C, 0, 1)
+            h = collision_h.collision(dx=dx, dt=dt, f=h, rho=C, vel=C_vel, flags=C_flags, force=None,
+                                      mesh_grid=mesh_grid, is_convection=True, KBC_type=int(api.KBCType.KBC_C))
         for y0, series in ((walks_int, inflow), (walks_int + 1, current)):
             dC_z = ((C)[..., y0, 0:radius_obs_int] - (C)[..., y0 - 1, 0:radius_obs_int]).flatten()
             r = mesh_grid[..., 0:1, y0, 0:radius_obs_int + 1].flatten()

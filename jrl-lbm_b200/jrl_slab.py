@@ -1,0 +1,161 @@
+"""Row-slab decomposition of one lattice across the GPUs of a node.
+
+The reference is single-device (no nccl / mpi / torch.distributed anywhere); this is new work.
+One process per GPU.  Rank r owns global rows [row0, row0 + nrows) of every field and stores
+them as local rows 1..nrows of a [B, C, nrows + 2, W] tensor; local rows 0 and nrows + 1 are
+ghost rows holding the neighbour ranks' edge rows.  Streaming is a radius-1 stencil, so ONE
+exchange of the post-collision populations' edge rows per step is the only communication; the
+periodic wrap of FLUID cells (propagation.cu:86-87) makes the rank topology a ring.
+
+Per step (CUDA):   main stream : update the two edge rows -> record E
+                   comm stream : wait E, pack edge rows, ncclSend/ncclRecv both neighbours, unpack
+                   main stream : update the interior rows (overlaps the exchange), then wait comm
+The exchange moves 2 x 9 x W fp32 per rank per step (2.4 MB at W = 32768) against
+72 B x nrows x W of HBM traffic for the interior, so it hides completely behind the interior.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+import jrl_native as N
+
+
+def slab_rows(H, world, rank):
+    """Contiguous, near-equal split of H rows: (row0, nrows) of `rank`."""
+    base, rem = divmod(H, world)
+    n = base + (1 if rank < rem else 0)
+    row0 = rank * base + min(rank, rem)
+    return row0, n
+
+
+class SlabLattice:
+    def __init__(self, fused, H, W, rank=None, world=None, device=None, group=None, B=1, overlap=True):
+        self.fs = fused
+        self.H, self.W, self.B = int(H), int(W), int(B)
+        self.group = group
+        self.rank = dist.get_rank(group) if rank is None else rank
+        self.world = dist.get_world_size(group) if world is None else world
+        self.device = torch.device(device)
+        self.row0, self.nrows = slab_rows(self.H, self.world, self.rank)
+        if self.nrows < 3:
+            raise RuntimeError("a slab needs at least 3 rows per rank")
+        self.prev = (self.rank - 1) % self.world
+        self.next = (self.rank + 1) % self.world
+        self.cuda = self.device.type == "cuda"
+        self.overlap = overlap and self.cuda
+        self.comm_stream = torch.cuda.Stream(self.device, priority=-1) if self.overlap else None
+        self._staging = {}
+        self.f = None       # current populations  [B,9,nrows+2,W]
+        self.f_next = None  # double buffer
+        self.fields = {}    # name -> slab tensor of the static / per-step inputs (flags, phi_obs, vel, ...)
+
+    # -- storage ---------------------------------------------------------------------------------
+    def empty(self, C, dtype=torch.float32):
+        return torch.empty((self.B, C, self.nrows + 2, self.W), dtype=dtype, device=self.device)
+
+    def scatter_global(self, full, exchange=True):
+        """Slab (with ghost rows) of a global [B,C,H,W] tensor that every rank can index (tests and
+        small grids; large grids build their slab directly from a formula)."""
+        C = full.shape[1]
+        out = self.empty(C, full.dtype)
+        idx = torch.arange(self.row0 - 1, self.row0 + self.nrows + 1) % self.H
+        out.copy_(full[:, :, idx.to(full.device), :].to(self.device))
+        return out
+
+    def _moment_buffer(self, name, C):
+        if name not in self._staging:
+            self._staging[name] = self.empty(C)
+        return self._staging[name]
+
+    def owned(self, slab):
+        return slab[:, :, 1:self.nrows + 1, :]
+
+    # -- halo exchange ---------------------------------------------------------------------------
+    def _stage(self, C, dtype, key):
+        k = (C, dtype, key)
+        if k not in self._staging:
+            self._staging[k] = torch.empty((self.B * C, 1, self.W), dtype=dtype, device=self.device)
+        return self._staging[k]
+
+    def _pack(self, field, row, staging):
+        BC = field.shape[0] * field.shape[1]
+        if field.dtype == torch.float32:
+            N.call("jrl_halo_pack_f32", ctypes.c_void_p(field.data_ptr()), ctypes.c_void_p(staging.data_ptr()),
+                   BC, self.nrows + 2, self.W, row, 1, like=field)
+        else:
+            staging.copy_(field.reshape(BC, self.nrows + 2, self.W)[:, row:row + 1, :])
+
+    def _unpack(self, field, row, staging):
+        BC = field.shape[0] * field.shape[1]
+        if field.dtype == torch.float32:
+            N.call("jrl_halo_unpack_f32", ctypes.c_void_p(field.data_ptr()), ctypes.c_void_p(staging.data_ptr()),
+                   BC, self.nrows + 2, self.W, row, 1, like=field)
+        else:
+            field.reshape(BC, self.nrows + 2, self.W)[:, row:row + 1, :].copy_(staging)
+
+    def exchange(self, field):
+        """Fill `field`'s two ghost rows from the neighbour ranks' edge rows (ring)."""
+        C = field.shape[1]
+        n = self.nrows
+        up, down = self._stage(C, field.dtype, "s_up"), self._stage(C, field.dtype, "s_down")
+        self._pack(field, n, up)      # my last owned row  -> next rank's ghost row 0
+        self._pack(field, 1, down)    # my first owned row -> prev rank's ghost row n+1
+        if self.world == 1:
+            self._unpack(field, 0, up)
+            self._unpack(field, n + 1, down)
+            return
+        r_lo, r_hi = self._stage(C, field.dtype, "r_lo"), self._stage(C, field.dtype, "r_hi")
+        ops = [dist.P2POp(dist.isend, up, self._peer(self.next), self.group, tag=1),
+               dist.P2POp(dist.isend, down, self._peer(self.prev), self.group, tag=2),
+               dist.P2POp(dist.irecv, r_lo, self._peer(self.prev), self.group, tag=1),
+               dist.P2POp(dist.irecv, r_hi, self._peer(self.next), self.group, tag=2)]
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        self._unpack(field, 0, r_lo)
+        self._unpack(field, n + 1, r_hi)
+
+    def _peer(self, group_rank):
+        return group_rank if self.group is None else dist.get_global_rank(self.group, group_rank)
+
+    # -- time stepping -----------------------------------------------------------------------------
+    def set_state(self, f_slab, **fields):
+        """f_slab: [B,9,nrows+2,W] with valid owned rows; ghost rows are filled here.  `fields`:
+        slab tensors passed to FusedStep.step by keyword (flags required; rho, vel, phi_obs, force,
+        mesh_grid, obs_vel ... as the configuration needs), ghost rows already valid."""
+        self.f = f_slab
+        self.f_next = torch.empty_like(f_slab)
+        self.fields = dict(fields)
+        self.exchange(self.f)
+
+    def step(self, **kw):
+        """One lattice update of the whole distributed grid; returns this rank's new slab."""
+        fs, r0, n = self.fs, self.row0, self.nrows
+        args = dict(self.fields)
+        args.update(kw)
+        flags = args.pop("flags")
+        rho, vel = args.pop("rho", None), args.pop("vel", None)
+        store = args.pop("store_moments", False)
+        if store:  # the three launches of a step share one pair of moment buffers
+            if "rho_out" not in args:
+                args["rho_out"] = self._moment_buffer("rho_out", 1)
+            if "vel_out" not in args and not fs.is_convection:
+                args["vel_out"] = self._moment_buffer("vel_out", 2)
+        common = dict(f_out=self.f_next, slab=(r0, n, self.H), store_moments=store, **args)
+        # 1. edge rows first: they are what the neighbours wait for
+        fs.step(self.f, flags, rho, vel, rows=(r0, r0 + 1), **common)
+        fs.step(self.f, flags, rho, vel, rows=(r0 + n - 1, r0 + n), **common)
+        if self.overlap:
+            main = torch.cuda.current_stream(self.device)
+            self.comm_stream.wait_stream(main)
+            with torch.cuda.stream(self.comm_stream):
+                self.exchange(self.f_next)
+            fs.step(self.f, flags, rho, vel, rows=(r0 + 1, r0 + n - 1), **common)  # 2. interior overlaps the exchange
+            main.wait_stream(self.comm_stream)
+        else:
+            fs.step(self.f, flags, rho, vel, rows=(r0 + 1, r0 + n - 1), **common)
+            self.exchange(self.f_next)
+        self.f, self.f_next = self.f_next, self.f
+        return self.f

@@ -1,0 +1,112 @@
+"""The fused lattice update behind one call: jrl_step_f32 (include/jrl_lbm.h).
+
+One launch = prop.propagation -> [coupling.solve_boundary] -> macro.macro_compute(_C) ->
+collision.collision of the reference's demo loops (demo_2d_LBM.py:101-119,
+demo_2d_LBM_cylinder.py:138-172, demo_2d_LBM_JRL_C_cylinder.py:313-326), bit-identical to
+calling the four solver objects in that order, at 72 B of population traffic per lattice
+update instead of four full passes.  The axisymmetric FLUID collision (JRL stage A) needs
+neighbours' post-stream moments and is the one combination that stays on the solver-object
+path (the library rejects it).
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+
+import torch
+
+import jrl_native as N
+from jrl_solver import _KBC_CODES, _dims, _full, mrt_operator
+
+_OPS = {"bgk": N.OP_BGK, "mrt": N.OP_MRT, "kbc": N.OP_KBC}
+
+
+class FusedStep:
+    """Configured once per run (operator, tau, symmetry, contact angle); `step()` per time step.
+
+    parameters : SimulationParameters (tau, axisymmetric_type, contact_angle are read)
+    operator   : 'bgk' | 'mrt' | 'kbc'
+    is_convection : advection-diffusion form for the concentration field (BGK, relaxation tau_D)
+    """
+
+    def __init__(self, parameters, operator="bgk", kbc_type=None, tau=None, tau_D=None, is_convection=False,
+                 dx=1.0, dt=1.0, contact_angle="from_parameters"):
+        self.axisymmetric_type = int(parameters.axisymmetric_type)
+        self.op = _OPS[operator]
+        self.kbc_type = 0 if kbc_type is None else int(kbc_type)
+        if self.op == N.OP_KBC and self.kbc_type not in _KBC_CODES:
+            raise RuntimeError("Please specific a right KBC Type value")
+        self.is_convection = bool(is_convection)
+        if self.is_convection and self.op != N.OP_BGK:
+            raise RuntimeError("the concentration step is BGK only (LBM_collision_MRT_2d.py:138)")
+        self.tau = float(parameters.tau if tau is None else tau)
+        if self.is_convection:
+            if tau_D is None:
+                raise RuntimeError("is_convection needs tau_D")
+            self.tau = float(tau_D)
+        self.dx, self.dt = float(dx), float(dt)
+        self._mrt = mrt_operator(self.tau) if self.op == N.OP_MRT else None
+        ca = parameters.contact_angle if isinstance(contact_angle, str) else contact_angle
+        self.use_contact = (ca is not None) and not self.is_convection
+        if self.use_contact:
+            if isinstance(ca, torch.Tensor):
+                self.contact_tan = float(torch.tan(math.pi / 2.0 - ca.detach().to("cpu", torch.float32).reshape(-1)[0]))
+            else:
+                self.contact_tan = math.tan(math.pi / 2.0 - float(ca))
+        else:
+            self.contact_tan = 0.0
+
+    def step(self, f, flags, rho=None, vel=None, *, f_out=None, rho_out=None, vel_out=None, store_moments=True,
+             phi_obs=None, force=None, mesh_grid=None, inflow_vel=None, inflow_density=None, use_wall=False,
+             obs_vel=None, wall_phi=None, clamp01=False, slab=None, rows=None, force_vec=0):
+        """One lattice update f -> f_out.  Returns (f_out, rho_out, vel_out) for the fluid form and
+        (h_out, C_out) for the concentration form (`rho` is C, `vel` the advecting velocity).
+        Outputs are allocated when not given (pass your own ping-pong buffers to avoid that);
+        store_moments=False skips the rho/vel stores (pure 72 B/LUP path).
+        slab = (row0, nrows, H): tensors are [B,C,nrows+2,W] row slabs of a global H-row grid, with
+        ghost rows (multi-GPU); wall_phi: phi_obs for the wall step when streaming runs without it;
+        rows = (begin, end): update only these global rows."""
+        B, Hs, W = _dims(f)
+        H = Hs
+        d = N.StepDesc()
+        if slab is not None:
+            d.slab_row0, d.slab_rows, H = int(slab[0]), int(slab[1]), int(slab[2])
+            if Hs != d.slab_rows + 2:
+                raise RuntimeError("slab tensors must hold nrows + 2 rows")
+        if rows is not None:
+            d.row_begin, d.row_end = int(rows[0]), int(rows[1])
+        d.B, d.H, d.W = B, H, W
+        d.axisym = self.axisymmetric_type
+        d.op, d.kbc_type, d.is_convection = self.op, self.kbc_type, int(self.is_convection)
+        d.use_contact, d.contact_tan = int(self.use_contact), self.contact_tan
+        d.clamp01 = int(bool(clamp01))
+        d.dx, d.dt, d.tau = self.dx, self.dt, self.tau
+        d.mrt = self._mrt.data_ptr() if self._mrt is not None else None
+        d.flags = N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, Hs, W), like=f)
+        d.f_in = N.tensor_ptr(f, "f", shape=(B, 9, Hs, W))
+        if f_out is None:
+            f_out = torch.empty_like(f)
+        d.f_out = N.tensor_ptr(f_out, "f_out", shape=(B, 9, Hs, W), like=f)
+        d.phi_obs = N.tensor_ptr(phi_obs, "phi_obs", shape=(B, 1, Hs, W), like=f, optional=True)
+        d.rho = N.tensor_ptr(rho, "rho", shape=(B, 1, Hs, W), like=f, optional=True)
+        d.vel = N.tensor_ptr(vel, "vel", shape=(B, 2, Hs, W), like=f, optional=True)
+        if store_moments or self.use_contact:
+            if rho_out is None:
+                rho_out = torch.empty((B, 1, Hs, W), dtype=f.dtype, device=f.device)
+            if vel_out is None and not self.is_convection:
+                vel_out = torch.empty((B, 2, Hs, W), dtype=f.dtype, device=f.device)
+        d.rho_out = N.tensor_ptr(rho_out, "rho_out", shape=(B, 1, Hs, W), like=f, optional=True)
+        d.vel_out = N.tensor_ptr(vel_out, "vel_out", shape=(B, 2, Hs, W), like=f, optional=True)
+        force = _full(force, (B, 2, Hs, W), "force", f)
+        d.force = N.tensor_ptr(force, "force", shape=(B, 2, Hs, W), like=f, optional=True)
+        d.mesh_grid = N.tensor_ptr(mesh_grid, "mesh_grid", shape=(B, 2, Hs, W), like=f, optional=True)
+        d.inflow_vel = N.tensor_ptr(inflow_vel, "inflow_vel", shape=(2,), like=f, optional=True)
+        d.inflow_density = -1.0 if inflow_density is None else float(inflow_density)
+        d.use_wall = int(bool(use_wall))
+        d.obs_vel = N.tensor_ptr(obs_vel, "obs_vel", shape=(B, 2, Hs, W), like=f, optional=True)
+        d.force_vec = int(force_vec)
+        d.wall_phi = N.tensor_ptr(wall_phi, "wall_phi", shape=(B, 1, Hs, W), like=f, optional=True)
+        N.call("jrl_step_f32", ctypes.byref(d), like=f)
+        if self.is_convection:
+            return f_out, rho_out
+        return f_out, rho_out, vel_out

@@ -1,0 +1,34 @@
+"""Fused-step cases shared by the CPU (host-emulation) and GPU test modules: each entry runs a
+scenario twice -- through the four solver objects and through ONE jrl_step_f32 launch per step --
+and the results must agree bit for bit."""
+import numpy as np
+
+import jrl_scenarios as S
+
+FUSED_CASES = {
+    "shear_bgk": ("shear_layer", dict(res=(40, 32), steps=25, operator="bgk")),
+    "shear_bgk_odd": ("shear_layer", dict(res=(21, 19), steps=10, operator="bgk")),       # VEC = 1 path
+    "shear_bgk_w2": ("shear_layer", dict(res=(16, 22), steps=10, operator="bgk")),        # VEC = 2 path
+    "shear_mrt": ("shear_layer", dict(res=(24, 32), steps=20, operator="mrt", kbc_type=133)),
+    "shear_kbc_a": ("shear_layer", dict(res=(24, 24), steps=10, operator="kbc", kbc_type=133)),
+    "shear_kbc_d": ("shear_layer", dict(res=(24, 24), steps=10, operator="kbc", kbc_type=138)),
+    "cylinder": ("cylinder", dict(res=(64, 48), D=8, steps=40, center=(24.0, 22.0))),
+    "conc": ("jrl_conc", dict(res=(48, 32), balance_steps=15, walk_steps=40, radius_obs=2.50000000000001,
+                              inflow_height=8.50000000000001, Rg=3, vel_obs_conv=0.03)),
+    "conc_positive": ("jrl_conc", dict(res=(40, 28), balance_steps=5, walk_steps=20, radius_obs=2.50000000000001,
+                                       inflow_height=8.50000000000001, Rg=3, vel_obs_conv=0.03, is_negative=False,
+                                       clamp=False)),
+}
+
+
+def run_pair(api, device, name):
+    fn, kw = FUSED_CASES[name]
+    chain = getattr(S, fn)(api, device, **kw)
+    fused = getattr(S, fn)(api, device, fused=True, **kw)
+    return chain, fused
+
+
+def assert_identical(chain, fused):
+    for k, w in chain.items():
+        if isinstance(w, np.ndarray):
+            assert np.array_equal(np.asarray(fused[k]), w, equal_nan=True), f"{k}: fused step differs from the operator chain"

@@ -9,12 +9,12 @@ CASES = {
     # C2: demo_2d_LBM_KBC.py as shipped (MRT, KBC flag ignored) ...
     "c2_shear_mrt": ("shear_layer", dict(res=(40, 32), steps=60, operator="mrt", kbc_type=133)),
     # ... and as the config's wording asks (entropic KBC), all four variants
-    "c2_shear_kbc_a": ("shear_layer", dict(res=(32, 32), steps=20, operator="kbc", kbc_type=133)),
-    "c2_shear_kbc_b": ("shear_layer", dict(res=(32, 32), steps=20, operator="kbc", kbc_type=134)),
-    "c2_shear_kbc_c": ("shear_layer", dict(res=(32, 32), steps=20, operator="kbc", kbc_type=137)),
-    "c2_shear_kbc_d": ("shear_layer", dict(res=(32, 32), steps=20, operator="kbc", kbc_type=138)),
+    "c2_shear_kbc_a": ("shear_layer", dict(res=(32, 32), steps=12, operator="kbc", kbc_type=133)),
+    "c2_shear_kbc_b": ("shear_layer", dict(res=(32, 32), steps=12, operator="kbc", kbc_type=134)),
+    "c2_shear_kbc_c": ("shear_layer", dict(res=(32, 32), steps=12, operator="kbc", kbc_type=137)),
+    "c2_shear_kbc_d": ("shear_layer", dict(res=(32, 32), steps=12, operator="kbc", kbc_type=138)),
     # C3: demo_2d_LBM_cylinder.py scaled down (H=96, W=48, D=8)
-    "c3_cylinder": ("cylinder", dict(res=(96, 48), D=8, steps=120, center=(24.0, 30.0), snapshots=(20,))),
+    "c3_cylinder": ("cylinder", dict(res=(96, 48), D=8, steps=60, center=(24.0, 30.0), snapshots=(20,))),
     # C4/C5 stage A: axisymmetric moving-tip flow, with and without gravity; fast tip so it crosses cells
     "c5_jrl_fluid_g": ("jrl_fluid", dict(res=(48, 32), steps=80, radius_obs=2.50000000000001,
                                         inflow_height=8.50000000000001, Rg=3, vel_obs=0.02,

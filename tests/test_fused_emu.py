@@ -1,0 +1,11 @@
+"""CPU (host-emulated kernels): the fused single-launch step equals the solver-object chain."""
+import pytest
+import torch
+
+from fused_cases import FUSED_CASES, assert_identical, run_pair
+
+
+@pytest.mark.parametrize("name", list(FUSED_CASES))
+def test_fused_equals_chain(emu_api, name):
+    chain, fused = run_pair(emu_api, torch.device("cpu"), name)
+    assert_identical(chain, fused)

@@ -1,0 +1,114 @@
+"""GPU (-m gpu): the CUDA library, called through the drop-in `src.LBM` API and the C ABI, against
+  (a) the golden fixtures written by the REFERENCE's own Python classes (oracle/gen_golden.py),
+  (b) the numpy oracle on the same seeded inputs,
+  (c) size-independent properties at bandwidth-bound sizes (fused == operator chain bit for bit,
+      mass conservation on the periodic all-FLUID grid).
+Tolerance: BASELINE.json north_star -- masks / integer outputs bit-exact, float fields within
+1e-5 relative L2 (util.REL_L2_TOL)."""
+import numpy as np
+import pytest
+import torch
+
+import jrl_scenarios as S
+from fused_cases import FUSED_CASES, assert_identical, run_pair
+from golden_cases import CASES
+from util import compare_outputs, load_golden, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda:0")
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_case_matches_reference_golden(cuda_api, dev, name):
+    fn, kw = CASES[name]
+    got = getattr(S, fn)(cuda_api, dev, **kw)
+    compare_outputs(got, load_golden(name))
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_case_matches_oracle(cuda_api, oracle_api, dev, name):
+    fn, kw = CASES[name]
+    got = getattr(S, fn)(cuda_api, dev, **kw)
+    want = getattr(S, fn)(oracle_api, torch.device("cpu"), **kw)
+    compare_outputs(got, {k: v for k, v in want.items() if v is not None})
+
+
+@pytest.mark.parametrize("name", list(FUSED_CASES))
+def test_fused_equals_chain(cuda_api, dev, name):
+    chain, fused = run_pair(cuda_api, dev, name)
+    assert_identical(chain, fused)
+
+
+@pytest.mark.parametrize("name", ["c1_shear_bgk", "c2_shear_mrt", "c3_cylinder", "c4_jrl_conc"])
+def test_fused_matches_reference_golden(cuda_api, dev, name):
+    fn, kw = CASES[name]
+    got = getattr(S, fn)(cuda_api, dev, fused=True, **kw)
+    skip = [k for k in load_golden(name) if k.startswith("snap_")]
+    compare_outputs(got, load_golden(name), skip=skip)
+
+
+def test_large_grid_fused_equals_chain_and_conserves_mass(cuda_api, dev):
+    """2048 x 2048 periodic shear layer (larger than L2 with both buffers: 2 x 151 MB): the fused
+    128-bit path equals the operator chain bit for bit, and total mass is conserved."""
+    kw = dict(res=(2048, 2048), steps=6, operator="bgk")
+    chain = S.shear_layer(cuda_api, dev, **kw)
+    fused = S.shear_layer(cuda_api, dev, fused=True, **kw)
+    for k in ("f", "rho", "vel"):
+        assert np.array_equal(chain[k], fused[k]), k
+    m0 = chain["f0"].astype(np.float64).sum()
+    m1 = fused["f"].astype(np.float64).sum()
+    assert abs(m1 - m0) / m0 < 1e-6
+
+
+def test_vector_widths_agree(cuda_api, dev):
+    """force_vec = 1 / 2 / 4 cells per thread give identical populations."""
+    import jrl_step
+    P = cuda_api.SimulationParameters(simulation_size=(1, 1, 96, 128), device=dev, tau=0.6, contact_angle=None)
+    st = S.random_state((96, 128), 7, dev, obstacles=True, io_cells=True)
+    fs = jrl_step.FusedStep(P, operator="bgk")
+    iv = torch.tensor([0.01, 0.02], device=dev)
+    outs = []
+    for v in (1, 2, 4):
+        f, r, u = fs.step(st["f"], st["flags"], st["rho"], st["vel"], phi_obs=st["phi"], force=st["force"],
+                          inflow_vel=iv, inflow_density=1.0, force_vec=v)
+        outs.append((f.cpu().numpy(), r.cpu().numpy(), u.cpu().numpy()))
+    for o in outs[1:]:
+        for a, b in zip(outs[0], o):
+            assert np.array_equal(a, b, equal_nan=True)
+
+
+def test_strip_flux_and_momentum_exchange(cuda_api, dev):
+    import jrl_solver
+    import lbm_oracle as O
+    g = torch.Generator().manual_seed(3)
+    C = torch.rand((1, 1, 40, 24), generator=g)
+    mesh = cuda_api.create_2d_meshgrid_tensor((1, 1, 40, 24), dtype=torch.float32) + 0.5
+    out = jrl_solver.strip_flux(C.to(dev), mesh.to(dev), 9, 7).cpu().numpy()
+    assert abs(out[0] - O.strip_flux(C.numpy(), mesh.numpy(), 9, 7)) <= 1e-5 * abs(out[0])
+    assert abs(out[1] - O.strip_sum(C.numpy()[0, 0], 9, 7)) <= 1e-5 * abs(out[1])
+    st = S.random_state((33, 47), 5, dev)
+    F = jrl_solver.momentum_exchange(st["f"], st["flags"]).cpu().numpy()
+    Fo = O.momentum_exchange(st["f"].cpu().numpy(), st["flags"].cpu().numpy())
+    assert np.allclose(F, np.asarray(Fo), rtol=1e-10, atol=1e-10)
+
+
+def test_error_behaviour(cuda_api, dev):
+    """The reference checks nothing; the drop-in raises RuntimeError and never touches memory."""
+    P = cuda_api.SimulationParameters(simulation_size=(1, 1, 16, 16), device=dev)
+    R = cuda_api.SimulationRunner(P)
+    prop = R.create_propagation()
+    f = torch.zeros((1, 9, 16, 16), device=dev)
+    flags = torch.ones((1, 1, 16, 16), dtype=torch.uint8, device=dev)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        prop.propagation(f=f.cpu(), flags=flags.cpu())
+    with pytest.raises(RuntimeError, match="dtype"):
+        prop.propagation(f=f.double(), flags=flags)
+    with pytest.raises(RuntimeError, match="contiguous"):
+        prop.propagation(f=f.permute(0, 1, 3, 2), flags=flags)
+    with pytest.raises(RuntimeError, match="KBC Type"):
+        R.create_collision_KBC().collision(dx=1, dt=1, f=f, rho=f[:, :1].contiguous(), vel=f[:, :2].contiguous(),
+                                           flags=flags, force=None, KBC_type=7)
