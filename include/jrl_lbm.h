@@ -175,7 +175,9 @@ typedef struct jrl_step_desc
        slab's edge rows first, start the halo exchange, then update the interior);
        row_begin == row_end == 0: all stored rows. */
     int row_begin, row_end;
-    int force_vec;          /* 0 = widest cells-per-thread the extents/alignment allow; 1, 2, 4 */
+    int force_vec;          /* 0 = automatic (pipelined TMA kernel on wide grids, else the widest cells-per-thread
+                               the extents / alignment allow); 1, 2, 4 = register kernel with that many cells per
+                               thread; 8 = pipelined kernel (error if the grid is not eligible) */
     const float *wall_phi;  /* phi_obs seen by the moving-wall step; NULL: same as phi_obs.
                                (demo_2d_LBM_cylinder.py:139-157 streams WITHOUT phi_obs -- plain halfway
                                bounce-back -- but passes phi_obs to solve_boundary) */

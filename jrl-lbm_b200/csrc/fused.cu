@@ -87,105 +87,46 @@ struct VecIO<1>
     static __device__ __forceinline__ bool all_fluid(const uint8_t *p) { return *p == CT_FLUID; }
 };
 
-template <int VEC, int OP, int CONV>
-__global__ void __launch_bounds__(kThreads) k_step(const __grid_constant__ StepArgs a)
+// ---- streaming of one group of VEC cells by the generic path: every link rule, inflow / outflow,
+//      moving wall; reads global memory directly (lattice.cuh, stencil.cuh) ------------------------------
+template <int VEC>
+__device__ __forceinline__ void step_generic(const StepArgs &a, const Grid &g, long long b, int y, int x0,
+                                             float fc[VEC][9], uint8_t me[VEC])
 {
-    const Grid &g = a.g;
-    const int gpr = g.W / VEC;  // groups per row
-    const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gi >= (long long)(a.row_end - a.row_begin) * gpr)
-        return;
-    const int yl = (int)(gi / gpr);
-    const int y = a.row_begin + yl;
-    const int x0 = (int)(gi - (long long)yl * gpr) * VEC;
-    const long long b = blockIdx.y;
     const uint8_t *fl = a.flags + b * g.HW;
     const float *f = a.f_in + b * 9 * g.HW;
     const float *phi = a.phi ? a.phi + b * g.HW : nullptr;
     const float *rho = a.rho ? a.rho + b * g.HW : nullptr;
     const float *vel = a.vel ? a.vel + b * 2 * g.HW : nullptr;
-
-    // ---- classify the group -----------------------------------------------------------------
-    const int yn = y == 0 ? g.H - 1 : y - 1, yp = y + 1 == g.H ? 0 : y + 1;
-    const long long r0 = cell(g, y, y, 0), rn = cell(g, y, yn, 0), rp = cell(g, y, yp, 0);
-    const int xl = x0 == 0 ? g.W - 1 : x0 - 1, xr = x0 + VEC == g.W ? 0 : x0 + VEC;
-    bool bulk = !(g.axisym == AXI_X && x0 == 0) && !(g.axisym == AXI_Y && y == 0);
-    bulk = bulk && VecIO<VEC>::all_fluid(fl + r0 + x0) && VecIO<VEC>::all_fluid(fl + rn + x0) &&
-           VecIO<VEC>::all_fluid(fl + rp + x0);
-    bulk = bulk && fl[r0 + xl] == CT_FLUID && fl[r0 + xr] == CT_FLUID && fl[rn + xl] == CT_FLUID &&
-           fl[rn + xr] == CT_FLUID && fl[rp + xl] == CT_FLUID && fl[rp + xr] == CT_FLUID;
-
-    float fc[VEC][9];
-    uint8_t me[VEC];
-    if (bulk)
+    const long long r0 = cell(g, y, y, 0);
+    Inflow in;
+    in.rho = const_cast<float *>(a.rho);
+    in.vel = const_cast<float *>(a.vel);
+    in.inflow_vel = a.inflow_vel;
+    in.density = a.inflow_density;
+    in.has_density = a.has_inflow_density;
+#pragma unroll
+    for (int k = 0; k < VEC; ++k)
     {
-        // ---- streaming, bulk: out[q](x) = f[q](y - e_qy, x - e_qx), periodic ---------------------
-#pragma unroll
-        for (int q = 0; q < 9; ++q)
-        {
-            const int ex = JRL_EX(q), ey = JRL_EY(q);
-            const float *src = f + q * g.HW + (ey > 0 ? rn : (ey < 0 ? rp : r0));
-            float v[VEC];
-            if (VEC == 1)
-                v[0] = src[ex > 0 ? xl : (ex < 0 ? xr : x0)];
-            else
-            {
-                float t[VEC];
-                VecIO<VEC>::load(src + x0, t);
-                if (ex == 0)
-                {
-#pragma unroll
-                    for (int k = 0; k < VEC; ++k)
-                        v[k] = t[k];
-                }
-                else if (ex > 0)
-                {
-                    v[0] = src[xl];
-#pragma unroll
-                    for (int k = 1; k < VEC; ++k)
-                        v[k] = t[k - 1];
-                }
-                else
-                {
-#pragma unroll
-                    for (int k = 0; k < VEC - 1; ++k)
-                        v[k] = t[k + 1];
-                    v[VEC - 1] = src[xr];
-                }
-            }
-#pragma unroll
-            for (int k = 0; k < VEC; ++k)
-                fc[k][q] = v[k];
-        }
-#pragma unroll
-        for (int k = 0; k < VEC; ++k)
-            me[k] = CT_FLUID;
+        const int x = x0 + k;
+        me[k] = fl[r0 + x];
+        if (phi)
+            stream_cell<true, false>(g, f, fl, phi, in, const_cast<float *>(rho), const_cast<float *>(vel), y, x, fc[k]);
+        else
+            stream_cell<false, false>(g, f, fl, nullptr, in, const_cast<float *>(rho), const_cast<float *>(vel), y, x, fc[k]);
+        if (a.use_wall)
+            wall_cell(a.wp, g, fl, vel, a.wall_phi + b * g.HW, a.obs_vel ? a.obs_vel + b * 2 * g.HW : nullptr, y, x, fc[k],
+                      a.inflow_vel);
     }
-    else
-    {
-        // ---- streaming, generic: every link rule, inflow/outflow, moving wall --------------------
-        Inflow in;
-        in.rho = const_cast<float *>(a.rho);
-        in.vel = const_cast<float *>(a.vel);
-        in.inflow_vel = a.inflow_vel;
-        in.density = a.inflow_density;
-        in.has_density = a.has_inflow_density;
-#pragma unroll
-        for (int k = 0; k < VEC; ++k)
-        {
-            const int x = x0 + k;
-            me[k] = fl[r0 + x];
-            if (phi)
-                stream_cell<true, false>(g, f, fl, phi, in, const_cast<float *>(rho), const_cast<float *>(vel), y, x, fc[k]);
-            else
-                stream_cell<false, false>(g, f, fl, nullptr, in, const_cast<float *>(rho), const_cast<float *>(vel), y, x, fc[k]);
-            if (a.use_wall)
-                wall_cell(a.wp, g, fl, vel, a.wall_phi + b * g.HW, a.obs_vel ? a.obs_vel + b * 2 * g.HW : nullptr, y, x, fc[k],
-                          a.inflow_vel);
-        }
-    }
+}
 
-    // ---- moments + collision ------------------------------------------------------------------------
+// ---- moments + collision + stores of one group whose post-stream populations are in fc ----------------
+template <int VEC, int OP, int CONV>
+__device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, long long b, int y, int x0, long long r0,
+                                            float fc[VEC][9], const uint8_t me[VEC], bool active)
+{
+    const float *rho = a.rho ? a.rho + b * g.HW : nullptr;
+    const float *vel = a.vel ? a.vel + b * 2 * g.HW : nullptr;
     float r_out[VEC], ux_out[VEC], uy_out[VEC];
 #pragma unroll
     for (int k = 0; k < VEC; ++k)
@@ -241,6 +182,8 @@ __global__ void __launch_bounds__(kThreads) k_step(const __grid_constant__ StepA
     }
 
     // ---- stores ----------------------------------------------------------------------------------------
+    if (!active)
+        return;
     float *fo = a.f_out + b * 9 * g.HW + r0 + x0;
 #pragma unroll
     for (int q = 0; q < 9; ++q)
@@ -260,18 +203,491 @@ __global__ void __launch_bounds__(kThreads) k_step(const __grid_constant__ StepA
     }
 }
 
+// ---- prefetch primitives -------------------------------------------------------------------------
+// The bulk path's loads are issued BEFORE the flag classification resolves (their addresses are
+// valid for every group: rows and columns wrap periodically), as `asm volatile` so that the
+// compiler neither sinks them into the bulk branch nor orders them behind the flag compare:
+// one DRAM round trip per thread instead of two (profiles/README.md, r1 first capture).
+// f_in is read-only for the whole launch (f_out never aliases it), hence ld.global.nc.
+#ifndef JRL_HOST_EMU
+template <int VEC>
+__device__ __forceinline__ void ldg_vec(const float *p, float v[VEC])
+{
+    if constexpr (VEC == 4)
+        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "l"(p));
+    else if constexpr (VEC == 2)
+        asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(v[0]), "=f"(v[1]) : "l"(p));
+    else
+        asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v[0]) : "l"(p));
+}
+__device__ __forceinline__ float ldg_f32_if(const float *p, bool pred)
+{
+    float v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\tmov.f32 %0, 0f00000000;\n\t@p ld.global.nc.f32 %0, [%1];\n\t}"
+                 : "=f"(v) : "l"(p), "r"((int)pred));
+    return v;
+}
+template <int VEC>
+__device__ __forceinline__ uint32_t ldg_flags(const uint8_t *p)
+{
+    uint32_t v;
+    if constexpr (VEC == 4)
+        asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    else if constexpr (VEC == 2)
+    {
+        unsigned short h;
+        asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(h) : "l"(p));
+        v = h;
+    }
+    else
+        asm volatile("ld.global.nc.u8 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint32_t ldg_u8_if(const uint8_t *p, bool pred)
+{
+    uint32_t v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\tmov.u32 %0, 1;\n\t@p ld.global.nc.u8 %0, [%1];\n\t}"
+                 : "=r"(v) : "l"(p), "r"((int)pred));
+    return v;
+}
+#endif
+
+#ifndef JRL_STEP_MIN_BLOCKS
+#define JRL_STEP_MIN_BLOCKS 2
+#endif
+
+template <int VEC, int OP, int CONV>
+__global__ void __launch_bounds__(kThreads, JRL_STEP_MIN_BLOCKS) k_step(const __grid_constant__ StepArgs a)
+{
+    // Thread -> cells: blockDim = (TX, TY), TX a multiple of 32 so that a warp never straddles rows;
+    // x-group = blockIdx.x * TX + threadIdx.x, row = row_begin + blockIdx.y * TY + threadIdx.y,
+    // batch element = blockIdx.z.  No integer division.
+    const Grid &g = a.g;
+    const int gpr = g.W / VEC;  // groups per row
+    int gx = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = a.row_begin + blockIdx.y * blockDim.y + threadIdx.y;
+#ifdef JRL_HOST_EMU
+    if (gx >= gpr || y >= a.row_end)
+        return;
+    const bool active = true;
+#else
+    // Out-of-range threads stay in the warp (clamped to the last group / row, stores suppressed) so
+    // that the full-mask shuffles below are well defined.
+    const bool active = gx < gpr && y < a.row_end;
+    gx = min(gx, gpr - 1);
+    y = min(y, a.row_end - 1);
+#endif
+    const int x0 = gx * VEC;
+    const long long b = blockIdx.z;
+    const uint8_t *fl = a.flags + b * g.HW;
+    const float *f = a.f_in + b * 9 * g.HW;
+    const float *phi = a.phi ? a.phi + b * g.HW : nullptr;
+    const float *rho = a.rho ? a.rho + b * g.HW : nullptr;
+    const float *vel = a.vel ? a.vel + b * 2 * g.HW : nullptr;
+
+    const int yn = y == 0 ? g.H - 1 : y - 1, yp = y + 1 == g.H ? 0 : y + 1;
+    const long long r0 = cell(g, y, y, 0), rn = cell(g, y, yn, 0), rp = cell(g, y, yp, 0);
+    const int xl = x0 == 0 ? g.W - 1 : x0 - 1, xr = x0 + VEC == g.W ? 0 : x0 + VEC;
+    bool bulk = !(g.axisym == AXI_X && x0 == 0) && !(g.axisym == AXI_Y && y == 0);
+
+    float fc[VEC][9];
+    uint8_t me[VEC];
+#ifndef JRL_HOST_EMU
+    // ---- prefetch: 9 population vectors, the x-edge scalars only where no neighbour lane holds them,
+    //      3 flag words + edge flag bytes -- all in flight together ------------------------------------
+    const unsigned lane = threadIdx.x & 31u;
+    // lane-1 / lane+1 hold the x-adjacent group of the SAME row unless this group starts / ends the row
+    const bool own_l = lane == 0 || x0 == 0;
+    const bool own_r = lane == 31 || x0 + VEC == g.W;
+    float t[9][VEC];
+    float edge[9];
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+    {
+        const int ex = JRL_EX(q), ey = JRL_EY(q);
+        const float *src = f + q * g.HW + (ey > 0 ? rn : (ey < 0 ? rp : r0));
+        if (VEC == 1)
+            ldg_vec<1>(src + (ex > 0 ? xl : (ex < 0 ? xr : x0)), t[q]);
+        else
+        {
+            ldg_vec<VEC>(src + x0, t[q]);
+            if (ex > 0)
+                edge[q] = ldg_f32_if(src + xl, own_l);
+            else if (ex < 0)
+                edge[q] = ldg_f32_if(src + xr, own_r);
+        }
+    }
+    const uint32_t fluid_word = VEC == 4 ? 0x01010101u : (VEC == 2 ? 0x0101u : 0x01u);
+    const uint32_t w0 = ldg_flags<VEC>(fl + r0 + x0), wn = ldg_flags<VEC>(fl + rn + x0), wp = ldg_flags<VEC>(fl + rp + x0);
+    const bool e_l = VEC == 1 || own_l, e_r = VEC == 1 || own_r;
+    const uint32_t bl0 = ldg_u8_if(fl + r0 + xl, e_l), bln = ldg_u8_if(fl + rn + xl, e_l), blp = ldg_u8_if(fl + rp + xl, e_l);
+    const uint32_t br0 = ldg_u8_if(fl + r0 + xr, e_r), brn = ldg_u8_if(fl + rn + xr, e_r), brp = ldg_u8_if(fl + rp + xr, e_r);
+    // ---- classify: the whole 3 x (VEC + 2) neighbourhood must be FLUID.  Inside a warp the x-adjacent
+    //      columns belong to the neighbour lanes' groups, so "neighbour lane's 3 x VEC block is all
+    //      FLUID" (a superset of the two columns needed) is exchanged by shuffle; a group that fails
+    //      this stricter test only takes the generic path, which computes identical values.
+    const bool mine = w0 == fluid_word && wn == fluid_word && wp == fluid_word;
+    bool left_ok = bl0 == CT_FLUID && bln == CT_FLUID && blp == CT_FLUID;
+    bool right_ok = br0 == CT_FLUID && brn == CT_FLUID && brp == CT_FLUID;
+    if (VEC > 1)
+    {
+        const bool up = __shfl_up_sync(0xffffffffu, mine, 1), dn = __shfl_down_sync(0xffffffffu, mine, 1);
+        left_ok = own_l ? left_ok : up;
+        right_ok = own_r ? right_ok : dn;
+    }
+    bulk = bulk && mine && left_ok && right_ok;
+    // x-shifted directions: element x0-1 is the neighbour lane's last element, x0+VEC its first
+    if (VEC > 1)
+    {
+#pragma unroll
+        for (int q = 1; q < 9; ++q)
+        {
+            const int ex = JRL_EX(q);
+            if (ex > 0)
+            {
+                const float s = __shfl_up_sync(0xffffffffu, t[q][VEC - 1], 1);
+                edge[q] = own_l ? edge[q] : s;
+            }
+            else if (ex < 0)
+            {
+                const float s = __shfl_down_sync(0xffffffffu, t[q][0], 1);
+                edge[q] = own_r ? edge[q] : s;
+            }
+        }
+    }
+    if (bulk)
+    {
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
+        {
+            const int ex = JRL_EX(q);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k)
+            {
+                float v;
+                if (VEC == 1 || ex == 0)
+                    v = t[q][k];
+                else if (ex > 0)
+                    v = k == 0 ? edge[q] : t[q][k > 0 ? k - 1 : 0];
+                else
+                    v = k == VEC - 1 ? edge[q] : t[q][k < VEC - 1 ? k + 1 : 0];
+                fc[k][q] = v;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < VEC; ++k)
+            me[k] = CT_FLUID;
+    }
+#else
+    // ---- host emulation (tests only): classify, then plain loads ----------------------------------
+    bulk = bulk && VecIO<VEC>::all_fluid(fl + r0 + x0) && VecIO<VEC>::all_fluid(fl + rn + x0) &&
+           VecIO<VEC>::all_fluid(fl + rp + x0);
+    bulk = bulk && fl[r0 + xl] == CT_FLUID && fl[r0 + xr] == CT_FLUID && fl[rn + xl] == CT_FLUID &&
+           fl[rn + xr] == CT_FLUID && fl[rp + xl] == CT_FLUID && fl[rp + xr] == CT_FLUID;
+    if (bulk)
+    {
+        // out[q](x) = f[q](y - e_qy, x - e_qx), periodic
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
+        {
+            const int ex = JRL_EX(q), ey = JRL_EY(q);
+            const float *src = f + q * g.HW + (ey > 0 ? rn : (ey < 0 ? rp : r0));
+#pragma unroll
+            for (int k = 0; k < VEC; ++k)
+            {
+                const int x = x0 + k - ex;
+                fc[k][q] = src[x < 0 ? g.W - 1 : (x >= g.W ? 0 : x)];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < VEC; ++k)
+            me[k] = CT_FLUID;
+    }
+#endif
+    else
+        step_generic<VEC>(a, g, b, y, x0, fc, me);
+    step_finish<VEC, OP, CONV>(a, g, b, y, x0, r0, fc, me, active);
+}
+
+#ifndef JRL_HOST_EMU
+// =====================================================================================================
+// Pipelined variant for wide grids: persistent CTAs, TMA bulk copies (cp.async.bulk, SASS UBLKCP) into a
+// 2-stage shared-memory ring, completion on an mbarrier.
+//
+// Why: the register-prefetch kernel above keeps only (resident threads x 144 B) of loads in flight and
+// none while a thread is in its collision arithmetic; at 2 CTAs/SM it tops out near 4 TB/s while a plain
+// copy with the same access pattern reaches 6.7 TB/s (tools/membench.cu, profiles/README.md).  Here one
+// elected thread issues the NEXT tile's loads (9 direction rows + 3 flag rows, ~41 KB) as soon as the
+// stage's previous contents have been pulled into registers, so every CTA always has 1-2 tiles in
+// flight regardless of what its warps are doing: bytes in flight per SM are set by shared memory
+// (2 CTAs x 2 stages x 41 KB), not by registers or occupancy.
+//
+// Tile = one row segment of CW = 1024 cells (256 threads x 4 cells).  Direction q's buffer holds
+// f[q][y - e_qy][x0 - 4 .. x0 + cw + 4) so that the pull f[q](x - e_qx) is a shared-memory read at
+// offset -e_qx; the 4-float halos wrap periodically at the row ends (separate 16-byte copies there).
+// Groups whose 3 x 6 neighbourhood is not all FLUID (or that sit on a symmetry axis) ignore the staged
+// data and take step_generic(), exactly like k_step: both kernels produce identical bits.
+// Requirements (checked by the launcher): W % 16 == 0, W >= 1024, 16-byte aligned f_in / flags.
+// =====================================================================================================
+namespace pipe {
+
+constexpr int CW = 1024, HALO = 4, ROWF = CW + 2 * HALO, FHALO = 16, ROWB = CW + 2 * FHALO, STAGES = 2;
+
+struct Stage
+{
+    alignas(16) float f[9][ROWF];
+    alignas(16) uint8_t fl[3][ROWB];
+    alignas(8) unsigned long long full;  // mbarrier: tile landed
+    unsigned long long pad;
+};
+static_assert(sizeof(Stage) % 16 == 0, "stage stride must keep 16-byte alignment");
+
+__device__ __forceinline__ uint32_t s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(void *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void *bar, uint32_t parity)
+{
+    uint32_t ok = 0;
+    while (!ok)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(s32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, void *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(s32(dst)), "l"(src), "r"(bytes), "r"(s32(bar)) : "memory");
+}
+
+struct Tile
+{
+    int b, y, x0, cw;
+};
+
+__device__ __forceinline__ Tile tile_of(const StepArgs &a, unsigned t, unsigned tpr, unsigned rows)
+{
+    const unsigned R = t / tpr, c = t - R * tpr, b = R / rows;
+    Tile tl;
+    tl.b = (int)b;
+    tl.y = a.row_begin + (int)(R - b * rows);
+    tl.x0 = (int)c * CW;
+    tl.cw = min(CW, a.g.W - tl.x0);
+    return tl;
+}
+
+// one thread: arm the barrier and issue every bulk copy of tile `tl` into `st`
+__device__ __forceinline__ void issue_tile(const StepArgs &a, const Tile &tl, Stage &st)
+{
+    const Grid &g = a.g;
+    const int W = g.W, y = tl.y, x0 = tl.x0, cw = tl.cw;
+    const int yn = y == 0 ? g.H - 1 : y - 1, yp = y + 1 == g.H ? 0 : y + 1;
+    const long long row[3] = {cell(g, y, yn, 0), cell(g, y, y, 0), cell(g, y, yp, 0)};  // index = 1 - e_qy ... see below
+    const bool f_in = x0 >= HALO && x0 + cw + HALO <= W;      // halos contiguous with the segment
+    const bool b_in = x0 >= FHALO && x0 + cw + FHALO <= W;
+    const uint32_t fbytes = (uint32_t)(cw + 2 * HALO) * 4u, bbytes = (uint32_t)(cw + 2 * FHALO);
+    mbar_expect_tx(&st.full, 9u * fbytes - 3u * 2u * HALO * 4u + 3u * bbytes);  // the 3 e_qx == 0 directions carry no halo
+    const float *f = a.f_in + (long long)tl.b * 9 * g.HW;
+    const uint8_t *fl = a.flags + (long long)tl.b * g.HW;
+    const int xl = x0 == 0 ? W - HALO : x0 - HALO, xr = x0 + cw == W ? 0 : x0 + cw;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+    {
+        const int ex = JRL_EX(q), ey = JRL_EY(q);
+        const float *src = f + q * g.HW + row[ey > 0 ? 0 : (ey < 0 ? 2 : 1)];
+        if (ex == 0)
+            bulk_g2s(&st.f[q][HALO], src + x0, (uint32_t)cw * 4u, &st.full);
+        else if (f_in)
+            bulk_g2s(&st.f[q][0], src + x0 - HALO, fbytes, &st.full);
+        else
+        {
+            bulk_g2s(&st.f[q][HALO], src + x0, (uint32_t)cw * 4u, &st.full);
+            bulk_g2s(&st.f[q][0], src + xl, HALO * 4u, &st.full);
+            bulk_g2s(&st.f[q][HALO + cw], src + xr, HALO * 4u, &st.full);
+        }
+    }
+    const int bl = x0 == 0 ? W - FHALO : x0 - FHALO;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+    {
+        const uint8_t *src = fl + row[r];
+        if (b_in)
+            bulk_g2s(&st.fl[r][0], src + x0 - FHALO, bbytes, &st.full);
+        else
+        {
+            bulk_g2s(&st.fl[r][FHALO], src + x0, (uint32_t)cw, &st.full);
+            bulk_g2s(&st.fl[r][0], src + bl, FHALO, &st.full);
+            bulk_g2s(&st.fl[r][FHALO + cw], src + xr, FHALO, &st.full);
+        }
+    }
+}
+
+template <int OP, int CONV>
+__global__ void __launch_bounds__(kThreads, 2) k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, unsigned rows)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Stage *stages = reinterpret_cast<Stage *>(smem_raw);
+    const Grid &g = a.g;
+    const int tid = threadIdx.x;
+    if (tid == 0)
+    {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+            mbar_init(&stages[s].full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0)
+    {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+        {
+            const unsigned t = blockIdx.x + (unsigned)s * gridDim.x;
+            if (t < total)
+                issue_tile(a, tile_of(a, t, tpr, rows), stages[s]);
+        }
+    }
+    unsigned it = 0;
+    for (unsigned t = blockIdx.x; t < total; t += gridDim.x, ++it)
+    {
+        Stage &st = stages[it % STAGES];
+        const Tile tl = tile_of(a, t, tpr, rows);
+        const int x0 = tl.x0 + 4 * tid, y = tl.y;
+        const bool active = 4 * tid < tl.cw;
+        mbar_wait(&st.full, (it / STAGES) & 1u);
+        // ---- shared memory -> registers (everything this thread needs from the stage) ---------------
+        float t4[9][4], edge[9];
+        uint32_t w[3], el[3], er[3];
+        if (active)
+        {
+#pragma unroll
+            for (int q = 0; q < 9; ++q)
+            {
+                const float *row = &st.f[q][HALO + 4 * tid];
+                const float4 v = *reinterpret_cast<const float4 *>(row);
+                t4[q][0] = v.x; t4[q][1] = v.y; t4[q][2] = v.z; t4[q][3] = v.w;
+                const int ex = JRL_EX(q);
+                edge[q] = ex > 0 ? row[-1] : (ex < 0 ? row[4] : 0.f);
+            }
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+            {
+                const uint8_t *row = &st.fl[r][FHALO + 4 * tid];
+                w[r] = *reinterpret_cast<const uint32_t *>(row);
+                el[r] = row[-1];
+                er[r] = row[4];
+            }
+        }
+        __syncthreads();  // every thread has drained this stage
+        if (tid == 0)
+        {
+            const unsigned tn = t + (unsigned)STAGES * gridDim.x;
+            if (tn < total)
+                issue_tile(a, tile_of(a, tn, tpr, rows), st);
+        }
+        if (!active)
+            continue;
+        // ---- classify (rows: 0 = y-1, 1 = y, 2 = y+1) -------------------------------------------------
+        bool bulk = !(g.axisym == AXI_X && x0 == 0) && !(g.axisym == AXI_Y && y == 0);
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+            bulk = bulk && w[r] == 0x01010101u && el[r] == CT_FLUID && er[r] == CT_FLUID;
+        float fc[4][9];
+        uint8_t me[4];
+        const long long b = tl.b;
+        if (bulk)
+        {
+#pragma unroll
+            for (int q = 0; q < 9; ++q)
+            {
+                const int ex = JRL_EX(q);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    fc[k][q] = ex == 0 ? t4[q][k] : (ex > 0 ? (k == 0 ? edge[q] : t4[q][k > 0 ? k - 1 : 0])
+                                                            : (k == 3 ? edge[q] : t4[q][k < 3 ? k + 1 : 0]));
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                me[k] = CT_FLUID;
+        }
+        else
+            step_generic<4>(a, g, b, y, x0, fc, me);
+        step_finish<4, OP, CONV>(a, g, b, y, x0, cell(g, y, y, 0), fc, me, true);
+    }
+}
+
+template <int OP, int CONV>
+static int launch_one(const StepArgs &a, unsigned total, unsigned tpr, unsigned rows, cudaStream_t s)
+{
+    auto kern = k_step_pipe<OP, CONV>;
+    const size_t smem = sizeof(Stage) * STAGES;
+    static bool configured = false;  // per instantiation
+    if (!configured)
+    {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return JRL_ERR_CUDA;
+        configured = true;
+    }
+    const unsigned nb = min(total, (unsigned)(2 * sm_count()));
+    kern<<<nb, kThreads, smem, s>>>(a, total, tpr, rows);
+    return 0;
+}
+
+static bool eligible(const StepArgs &a, int B)
+{
+    const Grid &g = a.g;
+    if (g.W % 16 != 0 || g.W < CW)
+        return false;
+    if (((uintptr_t)a.f_in | (uintptr_t)a.flags | (uintptr_t)a.f_out) % 16 != 0)
+        return false;
+    if ((a.rho_out && (uintptr_t)a.rho_out % 16 != 0) || (a.vel_out && (uintptr_t)a.vel_out % 16 != 0))
+        return false;
+    const long long tiles = (long long)B * (a.row_end - a.row_begin) * ((g.W + CW - 1) / CW);
+    return tiles < (1ll << 31);
+}
+
+static int launch(const StepArgs &a, int B, cudaStream_t s)
+{
+    const unsigned tpr = (unsigned)((a.g.W + CW - 1) / CW), rows = (unsigned)(a.row_end - a.row_begin);
+    const unsigned total = (unsigned)B * rows * tpr;
+    if (a.cp.convection)
+        return a.g.axisym == AXI_X ? launch_one<OP_BGK, 1>(a, total, tpr, rows, s)
+                                   : (a.g.axisym == AXI_Y ? launch_one<OP_BGK, 2>(a, total, tpr, rows, s)
+                                                          : launch_one<OP_BGK, 3>(a, total, tpr, rows, s));
+    if (a.cp.op == OP_BGK)
+        return launch_one<OP_BGK, 0>(a, total, tpr, rows, s);
+    if (a.cp.op == OP_MRT)
+        return launch_one<OP_MRT, 0>(a, total, tpr, rows, s);
+    return launch_one<OP_KBC, 0>(a, total, tpr, rows, s);
+}
+
+}  // namespace pipe
+#endif  // !JRL_HOST_EMU
 
 template <int VEC>
 static int launch_step(const StepArgs &a, int B, cudaStream_t s)
 {
     const Grid &g = a.g;
-    const long long groups = (long long)(a.row_end - a.row_begin) * (g.W / VEC);
-    const dim3 grid(blocks_for(groups), (unsigned)B, 1);
+    const int gpr = g.W / VEC;
+    int tx = 32;
+    while (tx < gpr && tx < kThreads)
+        tx <<= 1;
+    const int ty = kThreads / tx;
+    const dim3 block(tx, ty, 1);
+    const int rows = a.row_end - a.row_begin;
+    const dim3 grid((gpr + tx - 1) / tx, (rows + ty - 1) / ty, (unsigned)B);
+    if (grid.y > 65535u || grid.z > 65535u)
+        return fail_arg("jrl_step_f32", "more than 65535 row blocks (or batch elements) in one launch: split it with row_begin / row_end");
 #define JRL_STEP(OPV, CONVV)                         \
     do                                               \
     {                                                \
         auto kern = k_step<VEC, OPV, CONVV>;         \
-        JRL_LAUNCH(kern, grid, kThreads, s, a);      \
+        JRL_LAUNCH(kern, grid, block, s, a);         \
     } while (0)
     if (a.cp.convection)
     {
@@ -373,17 +789,33 @@ extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream)
             break;
         }
     }
+#ifndef JRL_HOST_EMU
+    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4))
+    {
+        const bool ok = vec == 4 && pipe::eligible(a, d->B);
+        JRL_REQUIRE(ok || d->force_vec == 0, fn, "pipelined kernel needs W % 16 == 0, W >= 1024 and 16-byte aligned planes");
+        if (ok)
+        {
+            const int prc = pipe::launch(a, d->B, s);
+            if (prc != 0)
+                return prc;
+            if (d->use_contact)
+            {
+                const int ring = 2 * (d->H + d->W) - 4;
+                JRL_LAUNCH(k_contact_ring, dim3(blocks_for(ring, 128), d->B), 128, s, a.g, d->rho, d->flags, d->rho_out, d->contact_tan);
+            }
+            return check_launch(fn);
+        }
+    }
+#endif
     if (d->force_vec == 1 || d->force_vec == 2 || d->force_vec == 4)
     {
         JRL_REQUIRE(d->force_vec <= vec, fn, "force_vec wider than extents / alignment allow");
         vec = d->force_vec;
     }
-    if (vec == 4)
-        launch_step<4>(a, d->B, s);
-    else if (vec == 2)
-        launch_step<2>(a, d->B, s);
-    else
-        launch_step<1>(a, d->B, s);
+    const int rc = vec == 4 ? launch_step<4>(a, d->B, s) : (vec == 2 ? launch_step<2>(a, d->B, s) : launch_step<1>(a, d->B, s));
+    if (rc != 0)
+        return rc;
     if (d->use_contact)
     {
         const int ring = 2 * (d->H + d->W) - 4;

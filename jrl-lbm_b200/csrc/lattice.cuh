@@ -346,17 +346,32 @@ __device__ __forceinline__ void half_force_shift(float rho, float &ux, float &uy
 
 __device__ __forceinline__ void equilibrium(const EqParams &p, float rho, float ux, float uy, float feq[9])
 {
+    // Reference order (LBM_collision_2d.py:252-261), per direction q:
+    //   eu = (ux e_qx) c + (uy e_qy) c ;  feq = rho w (1 + eu/cs2) + rho w (0.5 eu eu /cs2 /cs2 - 0.5 uv /cs2)
+    // evaluated here once per OPPOSITE PAIR.  IEEE arithmetic is sign-symmetric, so with e in {-1,0,1}:
+    // (u * -1) * c == -(u * c), eu(opp q) == -eu(q), the quadratic term is identical for both members
+    // of a pair, and a zero term only affects the sign of a zero eu, which neither 1 + eu/cs2 nor
+    // eu * eu can see.  Finite inputs give bit-identical results to the per-direction form with
+    // roughly half the operations.
     const float uv = ux * ux + uy * uy;
     const float huv = (0.5f * uv) * p.inv_cs2;
-#pragma unroll
-    for (int q = 0; q < 9; ++q)
-    {
-        const float eu = (ux * (float)JRL_EX(q)) * p.c + (uy * (float)JRL_EY(q)) * p.c;
-        const float rw = rho * weight(q);
-        const float a = rw * (1.f + eu * p.inv_cs2);
-        const float b = rw * ((((0.5f * eu) * eu) * p.inv_cs2) * p.inv_cs2 - huv);
-        feq[q] = a + b;
-    }
+    const float uxc = ux * p.c, uyc = uy * p.c;
+    const float rw0 = rho * weight(0), rw1 = rho * weight(1), rw5 = rho * weight(5);
+    feq[0] = rw0 * 1.f + rw0 * (0.f - huv);
+#define JRL_FEQ_PAIR(q, qo, eu_expr, rw)                                            \
+    do                                                                              \
+    {                                                                               \
+        const float eu = (eu_expr);                                                 \
+        const float t1 = eu * p.inv_cs2;                                            \
+        const float bq = (rw) * ((((0.5f * eu) * eu) * p.inv_cs2) * p.inv_cs2 - huv); \
+        feq[q] = (rw) * (1.f + t1) + bq;                                            \
+        feq[qo] = (rw) * (1.f - t1) + bq;                                           \
+    } while (0)
+    JRL_FEQ_PAIR(1, 3, uxc, rw1);
+    JRL_FEQ_PAIR(2, 4, uyc, rw1);
+    JRL_FEQ_PAIR(5, 7, uxc + uyc, rw5);
+    JRL_FEQ_PAIR(8, 6, uxc - uyc, rw5);
+#undef JRL_FEQ_PAIR
 }
 
 // ------------------------------------------------------------------------------------------

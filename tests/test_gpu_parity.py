@@ -81,6 +81,36 @@ def test_vector_widths_agree(cuda_api, dev):
             assert np.array_equal(a, b, equal_nan=True)
 
 
+@pytest.mark.parametrize("op,conv,axisym", [("bgk", False, 0), ("mrt", False, 0), ("kbc", False, 0), ("bgk", True, 1),
+                                            ("bgk", True, 0)])
+@pytest.mark.parametrize("W", [1024, 2064])
+def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym, W):
+    """force_vec = 8 (TMA-pipelined kernel: 1024-cell tiles, partial last tile at W = 2064, halo wrap at
+    the row ends, mixed FLUID / obstacle / inlet groups) equals force_vec = 4 and 1 bit for bit."""
+    import jrl_step
+    H = 37
+    P = cuda_api.SimulationParameters(simulation_size=(1, 1, H, W), device=dev, tau=0.6, contact_angle=None,
+                                      axisymmetric_type=axisym)
+    st = S.random_state((H, W), 9, dev, obstacles=True, io_cells=True)
+    flags = st["flags"].clone()
+    flags[:, :, 8:30, 100:W - 100] = 1          # a large all-FLUID region so that the staged (bulk) path runs too
+    fs = jrl_step.FusedStep(P, operator=op, kbc_type=133 if op == "kbc" else None, is_convection=conv,
+                            tau_D=0.8 if conv else None)
+    mesh = cuda_api.create_2d_meshgrid_tensor((1, 1, H, W), device=dev) + 0.5
+    kw = dict(phi_obs=st["phi"], inflow_density=0.5)
+    if conv:
+        kw.update(mesh_grid=mesh, clamp01=True)
+    else:
+        kw.update(force=st["force"], inflow_vel=torch.tensor([0.01, 0.02], device=dev))
+    outs = []
+    for v in (8, 4, 1):
+        o = fs.step(st["f"], flags, st["rho"], st["vel"], force_vec=v, **kw)
+        outs.append([t.cpu().numpy() for t in o])
+    for o in outs[1:]:
+        for a, b in zip(outs[0], o):
+            assert np.array_equal(a, b, equal_nan=True)
+
+
 def test_strip_flux_and_momentum_exchange(cuda_api, dev):
     import jrl_solver
     import lbm_oracle as O
