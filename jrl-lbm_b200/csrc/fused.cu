@@ -128,6 +128,11 @@ __device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, lo
     const float *rho = a.rho ? a.rho + b * g.HW : nullptr;
     const float *vel = a.vel ? a.vel + b * 2 * g.HW : nullptr;
     float r_out[VEC], ux_out[VEC], uy_out[VEC];
+#ifdef JRL_EXP_NO_MATH  // experiment only (tools/): data movement without the arithmetic
+#pragma unroll
+    for (int k = 0; k < VEC; ++k)
+        r_out[k] = ux_out[k] = uy_out[k] = fc[k][0];
+#else
 #pragma unroll
     for (int k = 0; k < VEC; ++k)
     {
@@ -180,6 +185,7 @@ __device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, lo
             collide_cell<OP, CONV>(a.cp, r, ux, uy, a.force != nullptr, fx, fy, rr, nullptr, fc[k]);
         }
     }
+#endif
 
     // ---- stores ----------------------------------------------------------------------------------------
     if (!active)
@@ -432,14 +438,15 @@ __global__ void __launch_bounds__(kThreads, JRL_STEP_MIN_BLOCKS) k_step(const __
 // =====================================================================================================
 namespace pipe {
 
-constexpr int CW = 1024, HALO = 4, ROWF = CW + 2 * HALO, FHALO = 16, ROWB = CW + 2 * FHALO, STAGES = 2;
+constexpr int CW = 1024, HALO = 4, ROWF = CW + 2 * HALO, FHALO = 16, ROWB = CW + 2 * FHALO;
 
 struct Stage
 {
     alignas(16) float f[9][ROWF];
     alignas(16) uint8_t fl[3][ROWB];
     alignas(8) unsigned long long full;  // mbarrier: tile landed
-    unsigned long long pad;
+    unsigned int drained;                // threads that have pulled this fill into registers
+    unsigned int pad;
 };
 static_assert(sizeof(Stage) % 16 == 0, "stage stride must keep 16-byte alignment");
 
@@ -463,6 +470,16 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(s32(dst)), "l"(src), "r"(bytes), "r"(s32(bar)) : "memory");
+}
+
+// Counts a thread as done with a stage.  acq_rel at CTA scope: this thread's shared-memory reads of the
+// stage are performed before the increment becomes visible, and the thread that observes the final
+// count (and then lets the TMA engine overwrite the stage) is ordered after all of them.
+__device__ __forceinline__ unsigned drained_add(unsigned int *cnt)
+{
+    unsigned old;
+    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(s32(cnt)) : "memory");
+    return old;
 }
 
 struct Tile
@@ -527,9 +544,11 @@ __device__ __forceinline__ void issue_tile(const StepArgs &a, const Tile &tl, St
     }
 }
 
-template <int OP, int CONV>
-__global__ void __launch_bounds__(kThreads, 2) k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, unsigned rows)
+// VEC cells per thread (CW / VEC threads per CTA), STAGES ring slots, MINB CTAs per SM.
+template <int OP, int CONV, int VEC, int STAGES, int MINB>
+__global__ void __launch_bounds__(CW / VEC, MINB) k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, unsigned rows)
 {
+    constexpr int kThreadsP = CW / VEC;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Stage *stages = reinterpret_cast<Stage *>(smem_raw);
     const Grid &g = a.g;
@@ -538,7 +557,10 @@ __global__ void __launch_bounds__(kThreads, 2) k_step_pipe(const __grid_constant
     {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s)
+        {
             mbar_init(&stages[s].full, 1);
+            stages[s].drained = 0;
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -557,35 +579,36 @@ __global__ void __launch_bounds__(kThreads, 2) k_step_pipe(const __grid_constant
     {
         Stage &st = stages[it % STAGES];
         const Tile tl = tile_of(a, t, tpr, rows);
-        const int x0 = tl.x0 + 4 * tid, y = tl.y;
-        const bool active = 4 * tid < tl.cw;
+        const int x0 = tl.x0 + VEC * tid, y = tl.y;
+        const bool active = VEC * tid < tl.cw;
         mbar_wait(&st.full, (it / STAGES) & 1u);
         // ---- shared memory -> registers (everything this thread needs from the stage) ---------------
-        float t4[9][4], edge[9];
+        float tv[9][VEC], edge[9];
         uint32_t w[3], el[3], er[3];
         if (active)
         {
 #pragma unroll
             for (int q = 0; q < 9; ++q)
             {
-                const float *row = &st.f[q][HALO + 4 * tid];
-                const float4 v = *reinterpret_cast<const float4 *>(row);
-                t4[q][0] = v.x; t4[q][1] = v.y; t4[q][2] = v.z; t4[q][3] = v.w;
+                const float *row = &st.f[q][HALO + VEC * tid];
+                VecIO<VEC>::load(row, tv[q]);
                 const int ex = JRL_EX(q);
-                edge[q] = ex > 0 ? row[-1] : (ex < 0 ? row[4] : 0.f);
+                edge[q] = ex > 0 ? row[-1] : (ex < 0 ? row[VEC] : 0.f);
             }
 #pragma unroll
             for (int r = 0; r < 3; ++r)
             {
-                const uint8_t *row = &st.fl[r][FHALO + 4 * tid];
-                w[r] = *reinterpret_cast<const uint32_t *>(row);
+                const uint8_t *row = &st.fl[r][FHALO + VEC * tid];
+                w[r] = VEC == 4 ? *reinterpret_cast<const uint32_t *>(row) : (uint32_t) * reinterpret_cast<const uint16_t *>(row);
                 el[r] = row[-1];
-                er[r] = row[4];
+                er[r] = row[VEC];
             }
         }
-        __syncthreads();  // every thread has drained this stage
-        if (tid == 0)
+        // No block-wide barrier: whichever thread drains the stage LAST refills it, so warps run
+        // decoupled (a fast warp is held back only by the ring depth).
+        if (drained_add(&st.drained) == kThreadsP - 1)
         {
+            st.drained = 0;
             const unsigned tn = t + (unsigned)STAGES * gridDim.x;
             if (tn < total)
                 issue_tile(a, tile_of(a, tn, tpr, rows), st);
@@ -594,11 +617,12 @@ __global__ void __launch_bounds__(kThreads, 2) k_step_pipe(const __grid_constant
             continue;
         // ---- classify (rows: 0 = y-1, 1 = y, 2 = y+1) -------------------------------------------------
         bool bulk = !(g.axisym == AXI_X && x0 == 0) && !(g.axisym == AXI_Y && y == 0);
+        const uint32_t fluid_word = VEC == 4 ? 0x01010101u : 0x0101u;
 #pragma unroll
         for (int r = 0; r < 3; ++r)
-            bulk = bulk && w[r] == 0x01010101u && el[r] == CT_FLUID && er[r] == CT_FLUID;
-        float fc[4][9];
-        uint8_t me[4];
+            bulk = bulk && w[r] == fluid_word && el[r] == CT_FLUID && er[r] == CT_FLUID;
+        float fc[VEC][9];
+        uint8_t me[VEC];
         const long long b = tl.b;
         if (bulk)
         {
@@ -607,24 +631,24 @@ __global__ void __launch_bounds__(kThreads, 2) k_step_pipe(const __grid_constant
             {
                 const int ex = JRL_EX(q);
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    fc[k][q] = ex == 0 ? t4[q][k] : (ex > 0 ? (k == 0 ? edge[q] : t4[q][k > 0 ? k - 1 : 0])
-                                                            : (k == 3 ? edge[q] : t4[q][k < 3 ? k + 1 : 0]));
+                for (int k = 0; k < VEC; ++k)
+                    fc[k][q] = ex == 0 ? tv[q][k] : (ex > 0 ? (k == 0 ? edge[q] : tv[q][k > 0 ? k - 1 : 0])
+                                                            : (k == VEC - 1 ? edge[q] : tv[q][k < VEC - 1 ? k + 1 : 0]));
             }
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < VEC; ++k)
                 me[k] = CT_FLUID;
         }
         else
-            step_generic<4>(a, g, b, y, x0, fc, me);
-        step_finish<4, OP, CONV>(a, g, b, y, x0, cell(g, y, y, 0), fc, me, true);
+            step_generic<VEC>(a, g, b, y, x0, fc, me);
+        step_finish<VEC, OP, CONV>(a, g, b, y, x0, cell(g, y, y, 0), fc, me, true);
     }
 }
 
-template <int OP, int CONV>
-static int launch_one(const StepArgs &a, unsigned total, unsigned tpr, unsigned rows, cudaStream_t s)
+template <int OP, int CONV, int VEC, int STAGES, int MINB>
+static int launch_cfg(const StepArgs &a, unsigned total, unsigned tpr, unsigned rows, cudaStream_t s)
 {
-    auto kern = k_step_pipe<OP, CONV>;
+    auto kern = k_step_pipe<OP, CONV, VEC, STAGES, MINB>;
     const size_t smem = sizeof(Stage) * STAGES;
     static bool configured = false;  // per instantiation
     if (!configured)
@@ -633,9 +657,18 @@ static int launch_one(const StepArgs &a, unsigned total, unsigned tpr, unsigned 
             return JRL_ERR_CUDA;
         configured = true;
     }
-    const unsigned nb = min(total, (unsigned)(2 * sm_count()));
-    kern<<<nb, kThreads, smem, s>>>(a, total, tpr, rows);
+    const unsigned nb = min(total, (unsigned)(MINB * sm_count()));
+    kern<<<nb, CW / VEC, smem, s>>>(a, total, tpr, rows);
     return 0;
+}
+
+// Measured on B200 at 8192^2 BGK (tools/exp_step.py): 4 cells/thread, 2 stages, 2 CTAs/SM = 4.95 TB/s;
+// 5 stages with 1 CTA/SM (256 or 512 threads) = 4.1-4.3 TB/s (too few warps for the collision
+// arithmetic); 2 cells/thread at 2 CTAs/SM spills (64-register cap) = 3.6 TB/s.
+template <int OP, int CONV>
+static int launch_one(const StepArgs &a, unsigned total, unsigned tpr, unsigned rows, cudaStream_t s)
+{
+    return launch_cfg<OP, CONV, 4, 2, 2>(a, total, tpr, rows, s);
 }
 
 static bool eligible(const StepArgs &a, int B)
@@ -790,7 +823,9 @@ extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream)
         }
     }
 #ifndef JRL_HOST_EMU
-    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4))
+    // automatic choice: the pipelined kernel wins for BGK (memory-bound); MRT / KBC are bound by their
+    // arithmetic and run faster in the register kernel (3.8 vs 3.1 TB/s MRT at 8192^2)
+    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4 && d->op == JRL_OP_BGK))
     {
         const bool ok = vec == 4 && pipe::eligible(a, d->B);
         JRL_REQUIRE(ok || d->force_vec == 0, fn, "pipelined kernel needs W % 16 == 0, W >= 1024 and 16-byte aligned planes");

@@ -21,7 +21,7 @@ def run(lib, G=8192, steps=20, op="bgk"):
     f2 = torch.empty_like(f)
     flags = torch.ones((1, 1, G, G), dtype=torch.uint8, device=dev)
     out = {}
-    for vec in (8, 4, 2):
+    for vec in [int(v) for v in os.environ.get("VECS", "8,4,2").split(",")]:
         for _ in range(3):
             fs.step(f, flags, None, None, f_out=f2, store_moments=False, force_vec=vec); f, f2 = f2, f
         torch.cuda.synchronize()
