@@ -169,14 +169,14 @@ class Workload:
         self.step_no = 0
         self.cells = self.nrows * G
 
-    def step(self, flags=None):
+    def step(self, flags=None, sums=None):
         store = (self.step_no % OUT_EVERY) == OUT_EVERY - 1
         flags = self.flags if flags is None else flags
         if self.slab:
-            self.lat.step(flags=flags, store_moments=store, rho_out=self.rho_out, vel_out=self.vel_out) if store else \
-                self.lat.step(flags=flags)
+            self.lat.step(flags=flags, sums=sums, store_moments=store, rho_out=self.rho_out, vel_out=self.vel_out) if store else \
+                self.lat.step(flags=flags, sums=sums)
         else:
-            self.fs.step(self.f, flags, None, None, f_out=self.f2, store_moments=store,
+            self.fs.step(self.f, flags, None, None, f_out=self.f2, store_moments=store, sums=sums,
                          rho_out=self.rho_out if store else None, vel_out=self.vel_out if store else None)
             self.f, self.f2 = self.f2, self.f
         self.step_no += 1
@@ -237,6 +237,51 @@ def cpu_reference_run(G_full, steps, warmup, sample_grid=None, budget_s=20.0):
     info = {"value": mlups, "unit": UNIT, "cores": cores, "kind": kind,
             "sample": f"{Gs}x{Gs} periodic sub-problem of the {G_full}^2 shear layer (same formula and tau), {done} steps; {what}"}
     return mlups, info, dt / done * 1e3, done
+
+
+def run_e2e(wl, K, Wm, device, barrier):
+    """The same steps through the public API (FusedStep / SlabLattice) with HOST buffers in the loop:
+    every step uploads that step's flags field (uint8 [rows, G], authored on the host, pinned memory; a
+    host-driven moving obstacle rewrites it every step as the JRL demos do, demo_2d_LBM_JRL_fluid_
+    cylinder.py:212) and downloads the step's result, the mass / momentum sums reduced inside the step
+    kernel (jrl_step_desc.sums).  Uploads run one step ahead on a copy stream into a double buffer; the
+    downloads are asynchronous into a pinned ring and all have landed when the timed region closes.
+    Returns (seconds for K steps on this rank, h2d bytes/step, d2h bytes/step, host_sums[K,4])."""
+    import jrl_native
+    S = jrl_native.SUM_SLOTS
+    total = K + Wm
+    flags_host = torch.ones(wl.flags.shape, dtype=torch.uint8).pin_memory()
+    bufs = [torch.empty_like(wl.flags), torch.empty_like(wl.flags)]
+    copy_stream = torch.cuda.Stream(device)
+    main = torch.cuda.current_stream(device)
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+    sums = torch.zeros((total, S, 4), dtype=torch.float64, device=device)
+    host_sums = torch.empty((total, S, 4), dtype=torch.float64).pin_memory()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def upload(i):
+        with torch.cuda.stream(copy_stream):
+            if i >= 2:
+                copy_stream.wait_event(consumed[i % 2])
+            bufs[i % 2].copy_(flags_host, non_blocking=True)
+            ready[i % 2].record(copy_stream)
+
+    upload(0)
+    for i in range(total):
+        if i == Wm:
+            barrier()
+            e0.record()
+            upload(i)                    # the timed region holds all K uploads
+        if i + 1 < total and i + 1 != Wm:
+            upload(i + 1)
+        main.wait_event(ready[i % 2])
+        wl.step(flags=bufs[i % 2], sums=sums[i])
+        consumed[i % 2].record(main)
+        host_sums[i].copy_(sums[i], non_blocking=True)
+    e1.record()
+    barrier()
+    return e0.elapsed_time(e1) * 1e-3, flags_host.numel(), S * 4 * 8, host_sums[Wm:].sum(dim=1)
 
 
 def run_reference_arm(args):
@@ -311,10 +356,37 @@ def main():
     if not (mass_rel < 1e-4):
         raise SystemExit(f"bench.py: mass drifted by {mass_rel:.3e} -- the timed state is wrong")
 
+    e2e = None
+    if not args.no_e2e:
+        sec, h2d, d2h, hs = run_e2e(wl, K, Wm, device, barrier)
+        agg = torch.tensor([sec, float(h2d), float(d2h)], dtype=torch.float64, device=device)
+        mass_steps = hs[:, 0].to(device)
+        if world > 1:
+            t = agg[0:1].clone()
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(agg)
+            agg[0] = t[0]
+            dist.all_reduce(mass_steps)
+        worst = float((mass_steps / (RHO0 * G * G) - 1.0).abs().max().item())
+        if not (worst < 1e-4):
+            raise SystemExit(f"bench.py: e2e per-step mass read back from the device is off by {worst:.3e}")
+        e2e = {"value": G * G * K / float(agg[0].item()) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(agg[1].item()),
+               "d2h_bytes_per_step": int(agg[2].item()), "ms_per_step": float(agg[0].item()) / K * 1e3,
+               "what": "FusedStep/SlabLattice API; per step: H2D of the step's uint8 flags field from pinned host memory "
+                       "(prefetched one step ahead on a copy stream), one fused launch, D2H of the in-kernel mass/momentum "
+                       "sums (checked on the host: mass conserved to %.1e)" % worst}
+
     peak, peak_src = measured_peak()
+    traffic = None
+    try:  # DRAM bytes per lattice update of the dominant kernel from the committed ncu capture, scaled to this launch
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as fh:
+            traffic = float(json.load(fh)["dram_bytes_per_lup"]) * G * G / world
+    except Exception:
+        pass
     achieved = BYTES_PER_LUP * G * G / world / (ms_per_step * 1e-3) / 1e9   # per GPU: its cells / the step time
-    roofline = {"bound": "hbm", "kernel": "jrl::k_step<4, OP_BGK, 0> (jrl_step_f32)", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
+    roofline = {"bound": "hbm", "kernel": "jrl::pipe::k_step_pipe<OP_BGK, 0, 4, 2, 2> (jrl_step_f32)", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": traffic,
+                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum per lattice update at 8192^2 (profiles/r1_traffic.json) x cells of this launch",
                 "algorithmic_bytes_per_launch": BYTES_PER_LUP * G * G / world,
                 "note": "per GPU; 72 B per lattice update x cells per rank / CUDA-event step time (1 dominant launch per step)"}
     line = {"metric": METRIC, "value": mlups, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
@@ -323,7 +395,7 @@ def main():
             "config": {"workload": f"demo_2d_LBM.py double shear layer, D2Q9 BGK, periodic, {G}x{G} fp32 (BASELINE configs[4] strong-scaling grid)",
                        "grid": G, "tau": shear_tau(G), "rows_per_rank": wl.nrows, "decomposition": "row slabs, ring halo exchange (NCCL)" if world > 1 else "single domain",
                        "moments_stored_every": OUT_EVERY, "l2": "working set (2 x %.1f GB of populations per rank) is far larger than the 126 MB L2" % (36.0 * G * G / world / 1e9)},
-            "roofline": roofline, "gpu_launches": int(nl.item()), "mass_drift": mass_rel}
+            "roofline": roofline, "e2e": e2e, "gpu_launches": int(nl.item()), "mass_drift": mass_rel}
     if rank == 0:
         line["clocks"] = clocks.summary()
         if not args.no_cpu_baseline and world == 1:

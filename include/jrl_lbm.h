@@ -35,6 +35,7 @@ enum { JRL_CELL_NOTHING = 0, JRL_CELL_FLUID = 1, JRL_CELL_OBSTACLE = 2, JRL_CELL
        JRL_CELL_INFLOW = 8, JRL_CELL_OUTFLOW = 16, JRL_CELL_INFLOW_2 = 32 };
 enum { JRL_AXI_NOT = 0, JRL_AXI_X = 1, JRL_AXI_Y = 2 };
 enum { JRL_OP_BGK = 0, JRL_OP_MRT = 1, JRL_OP_KBC = 2 };
+#define JRL_SUM_SLOTS 64
 enum { JRL_KBC_LBGK = 0, JRL_KBC_A = 0x85, JRL_KBC_B = 0x86, JRL_KBC_C = 0x89, JRL_KBC_D = 0x8A };
 
 int jrl_version(void);
@@ -178,6 +179,11 @@ typedef struct jrl_step_desc
     int force_vec;          /* 0 = automatic (pipelined TMA kernel on wide grids, else the widest cells-per-thread
                                the extents / alignment allow); 1, 2, 4 = register kernel with that many cells per
                                thread; 8 = pipelined kernel (error if the grid is not eligible) */
+    double *sums;           /* NULL, or device [JRL_SUM_SLOTS][4] doubles that this launch ADDS to (caller zeroes):
+                               per slot {sum rho, sum rho u_x, sum rho u_y, cells} over the non-OBSTACLE cells it
+                               updated, with the post-stream moments (C, C u for the concentration form).  Warp-
+                               shuffle reduction inside the step kernel, one atomicAdd per warp spread over the
+                               slots; the total is the sum over slots (the mass / momentum diagnostic). */
     const float *wall_phi;  /* phi_obs seen by the moving-wall step; NULL: same as phi_obs.
                                (demo_2d_LBM_cylinder.py:139-157 streams WITHOUT phi_obs -- plain halfway
                                bounce-back -- but passes phi_obs to solve_boundary) */

@@ -27,6 +27,7 @@ struct StepArgs
     float *f_out;
     const float *phi;
     const float *wall_phi;
+    double *sums;
     const float *rho;  // previous-step density / concentration (kept at OBSTACLE cells)
     const float *vel;  // previous-step velocity, or the advecting velocity when convection
     float *rho_out;
@@ -123,7 +124,7 @@ __device__ __forceinline__ void step_generic(const StepArgs &a, const Grid &g, l
 // ---- moments + collision + stores of one group whose post-stream populations are in fc ----------------
 template <int VEC, int OP, int CONV>
 __device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, long long b, int y, int x0, long long r0,
-                                            float fc[VEC][9], const uint8_t me[VEC], bool active)
+                                            float fc[VEC][9], const uint8_t me[VEC], bool active, float acc[3])
 {
     const float *rho = a.rho ? a.rho + b * g.HW : nullptr;
     const float *vel = a.vel ? a.vel + b * 2 * g.HW : nullptr;
@@ -171,6 +172,9 @@ __device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, lo
         uy_out[k] = uy;
         if (!obs)
         {
+            acc[0] += r;
+            acc[1] += r * ux;
+            acc[2] += r * uy;
             float fx = 0.f, fy = 0.f;
             if (a.force)
             {
@@ -207,6 +211,39 @@ __device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, lo
         VecIO<VEC>::store(a.vel_out + b * 2 * g.HW + r0 + x0, ux_out);
         VecIO<VEC>::store(a.vel_out + b * 2 * g.HW + g.HW + r0 + x0, uy_out);
     }
+}
+
+// ---- R8-style diagnostic: {sum rho, sum rho ux, sum rho uy, cells} of the cells a launch updated ------
+// acc[] are this thread's fp32 partial sums (zero for threads without cells); warp-shuffle tree in
+// fp64, one atomicAdd per warp and quantity into slot (warp id mod JRL_SUM_SLOTS).
+__device__ __forceinline__ void add_sums(double *sums, const float acc[3], float cells)
+{
+#ifdef JRL_HOST_EMU
+    double *s = sums;  // slot 0
+#pragma omp atomic
+    s[0] += (double)acc[0];
+#pragma omp atomic
+    s[1] += (double)acc[1];
+#pragma omp atomic
+    s[2] += (double)acc[2];
+#pragma omp atomic
+    s[3] += (double)cells;
+#else
+    double v[4] = {(double)acc[0], (double)acc[1], (double)acc[2], (double)cells};
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            v[j] += __shfl_xor_sync(0xffffffffu, v[j], off);
+    if ((threadIdx.x & 31u) == 0)
+    {
+        const unsigned warp = ((blockIdx.x + 13u * blockIdx.y) * blockDim.y + threadIdx.y) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+        double *s = sums + 4 * (warp % JRL_SUM_SLOTS);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            atomicAdd(s + j, v[j]);
+    }
+#endif
 }
 
 // ---- prefetch primitives -------------------------------------------------------------------------
@@ -413,7 +450,18 @@ __global__ void __launch_bounds__(kThreads, JRL_STEP_MIN_BLOCKS) k_step(const __
 #endif
     else
         step_generic<VEC>(a, g, b, y, x0, fc, me);
-    step_finish<VEC, OP, CONV>(a, g, b, y, x0, r0, fc, me, active);
+    float acc[3] = {0.f, 0.f, 0.f};
+    step_finish<VEC, OP, CONV>(a, g, b, y, x0, r0, fc, me, active, acc);
+    if (a.sums)
+    {
+        float cells = 0.f;
+#pragma unroll
+        for (int k = 0; k < VEC; ++k)
+            cells += me[k] != CT_OBSTACLE ? 1.f : 0.f;
+        if (!active)
+            acc[0] = acc[1] = acc[2] = cells = 0.f;
+        add_sums(a.sums, acc, cells);
+    }
 }
 
 #ifndef JRL_HOST_EMU
@@ -613,8 +661,9 @@ __global__ void __launch_bounds__(CW / VEC, MINB) k_step_pipe(const __grid_const
             if (tn < total)
                 issue_tile(a, tile_of(a, tn, tpr, rows), st);
         }
-        if (!active)
-            continue;
+        float acc[3] = {0.f, 0.f, 0.f}, cells = 0.f;
+        if (active)
+        {
         // ---- classify (rows: 0 = y-1, 1 = y, 2 = y+1) -------------------------------------------------
         bool bulk = !(g.axisym == AXI_X && x0 == 0) && !(g.axisym == AXI_Y && y == 0);
         const uint32_t fluid_word = VEC == 4 ? 0x01010101u : 0x0101u;
@@ -641,7 +690,13 @@ __global__ void __launch_bounds__(CW / VEC, MINB) k_step_pipe(const __grid_const
         }
         else
             step_generic<VEC>(a, g, b, y, x0, fc, me);
-        step_finish<VEC, OP, CONV>(a, g, b, y, x0, cell(g, y, y, 0), fc, me, true);
+        step_finish<VEC, OP, CONV>(a, g, b, y, x0, cell(g, y, y, 0), fc, me, true, acc);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k)
+            cells += me[k] != CT_OBSTACLE ? 1.f : 0.f;
+        }
+        if (a.sums)
+            add_sums(a.sums, acc, cells);
     }
 }
 
@@ -790,6 +845,7 @@ extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream)
     a.f_out = d->f_out;
     a.phi = d->phi_obs;
     a.wall_phi = d->wall_phi ? d->wall_phi : d->phi_obs;
+    a.sums = d->sums;
     a.rho = d->rho;
     a.vel = d->vel;
     a.rho_out = d->rho_out;

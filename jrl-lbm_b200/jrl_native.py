@@ -25,6 +25,7 @@ _allow_cpu_tensors = False  # flipped only by _install_test_library (tests/host_
 
 AXI_NOT, AXI_X, AXI_Y = 0, 1, 2
 OP_BGK, OP_MRT, OP_KBC = 0, 1, 2
+SUM_SLOTS = 64
 
 
 class CollideDesc(Structure):  # struct jrl_collide_desc
@@ -42,7 +43,7 @@ class StepDesc(Structure):  # struct jrl_step_desc
                 ("vel", c_void_p), ("rho_out", c_void_p), ("vel_out", c_void_p), ("force", c_void_p),
                 ("mesh_grid", c_void_p), ("inflow_vel", c_void_p), ("inflow_density", c_double),
                 ("use_wall", c_int), ("obs_vel", c_void_p), ("slab_row0", c_int), ("slab_rows", c_int),
-                ("row_begin", c_int), ("row_end", c_int), ("force_vec", c_int), ("wall_phi", c_void_p)]
+                ("row_begin", c_int), ("row_end", c_int), ("force_vec", c_int), ("sums", c_void_p), ("wall_phi", c_void_p)]
 
 
 _vp, _i, _d, _f = c_void_p, c_int, c_double, c_float

@@ -58,14 +58,16 @@ class FusedStep:
 
     def step(self, f, flags, rho=None, vel=None, *, f_out=None, rho_out=None, vel_out=None, store_moments=True,
              phi_obs=None, force=None, mesh_grid=None, inflow_vel=None, inflow_density=None, use_wall=False,
-             obs_vel=None, wall_phi=None, clamp01=False, slab=None, rows=None, force_vec=0):
+             obs_vel=None, wall_phi=None, clamp01=False, slab=None, rows=None, force_vec=0, sums=None):
         """One lattice update f -> f_out.  Returns (f_out, rho_out, vel_out) for the fluid form and
         (h_out, C_out) for the concentration form (`rho` is C, `vel` the advecting velocity).
         Outputs are allocated when not given (pass your own ping-pong buffers to avoid that);
         store_moments=False skips the rho/vel stores (pure 72 B/LUP path).
         slab = (row0, nrows, H): tensors are [B,C,nrows+2,W] row slabs of a global H-row grid, with
         ghost rows (multi-GPU); wall_phi: phi_obs for the wall step when streaming runs without it;
-        rows = (begin, end): update only these global rows."""
+        rows = (begin, end): update only these global rows;
+        sums: float64 [SUM_SLOTS, 4] device tensor this launch adds {sum rho, sum rho ux, sum rho uy,
+        cells} to (see new_sums / total_sums)."""
         B, Hs, W = _dims(f)
         H = Hs
         d = N.StepDesc()
@@ -105,8 +107,19 @@ class FusedStep:
         d.use_wall = int(bool(use_wall))
         d.obs_vel = N.tensor_ptr(obs_vel, "obs_vel", shape=(B, 2, Hs, W), like=f, optional=True)
         d.force_vec = int(force_vec)
+        d.sums = N.tensor_ptr(sums, "sums", torch.float64, (N.SUM_SLOTS, 4), like=f, optional=True)
         d.wall_phi = N.tensor_ptr(wall_phi, "wall_phi", shape=(B, 1, Hs, W), like=f, optional=True)
         N.call("jrl_step_f32", ctypes.byref(d), like=f)
         if self.is_convection:
             return f_out, rho_out
         return f_out, rho_out, vel_out
+
+
+def new_sums(device):
+    """Zeroed accumulator for FusedStep.step(sums=...)."""
+    return torch.zeros((N.SUM_SLOTS, 4), dtype=torch.float64, device=device)
+
+
+def total_sums(sums):
+    """[mass, momentum_x, momentum_y, cells] as a device float64 [4] tensor (no host sync)."""
+    return sums.sum(dim=0)

@@ -32,3 +32,21 @@ def assert_identical(chain, fused):
     for k, w in chain.items():
         if isinstance(w, np.ndarray):
             assert np.array_equal(np.asarray(fused[k]), w, equal_nan=True), f"{k}: fused step differs from the operator chain"
+
+
+def check_sums(api, device, res=(40, 64), force_vec=0):
+    """FusedStep.step(sums=...) == sums of the stored moments over the non-OBSTACLE cells."""
+    import torch
+    import jrl_step
+    H, W = res
+    st = S.random_state(res, 21, device)
+    P = api.SimulationParameters(simulation_size=(1, 1, H, W), device=device, tau=0.7, contact_angle=None)
+    fs = jrl_step.FusedStep(P, operator="bgk")
+    sums = jrl_step.new_sums(device)
+    f, r, u = fs.step(st["f"], st["flags"], st["rho"], st["vel"], phi_obs=st["phi"], inflow_density=1.0, sums=sums,
+                      force_vec=force_vec)
+    tot = jrl_step.total_sums(sums).cpu().numpy()
+    fluid = (st["flags"] != 2).cpu().numpy()
+    r, u = r.cpu().numpy().astype(np.float64), u.cpu().numpy().astype(np.float64)
+    want = np.array([(r * fluid).sum(), (r * u[:, 0:1] * fluid).sum(), (r * u[:, 1:2] * fluid).sum(), fluid.sum()])
+    assert np.allclose(tot, want, rtol=2e-6, atol=1e-6), (tot, want)

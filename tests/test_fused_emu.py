@@ -2,10 +2,14 @@
 import pytest
 import torch
 
-from fused_cases import FUSED_CASES, assert_identical, run_pair
+from fused_cases import FUSED_CASES, assert_identical, check_sums, run_pair
 
 
 @pytest.mark.parametrize("name", list(FUSED_CASES))
 def test_fused_equals_chain(emu_api, name):
     chain, fused = run_pair(emu_api, torch.device("cpu"), name)
     assert_identical(chain, fused)
+
+
+def test_step_sums(emu_api):
+    check_sums(emu_api, torch.device("cpu"))

@@ -10,7 +10,7 @@ import pytest
 import torch
 
 import jrl_scenarios as S
-from fused_cases import FUSED_CASES, assert_identical, run_pair
+from fused_cases import FUSED_CASES, assert_identical, check_sums, run_pair
 from golden_cases import CASES
 from util import compare_outputs, load_golden, rel_l2
 
@@ -109,6 +109,11 @@ def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym
     for o in outs[1:]:
         for a, b in zip(outs[0], o):
             assert np.array_equal(a, b, equal_nan=True)
+
+
+@pytest.mark.parametrize("res,vec", [((40, 64), 0), ((21, 19), 0), ((24, 2048), 8), ((24, 2048), 4), ((24, 1040), 8)])
+def test_step_sums(cuda_api, dev, res, vec):
+    check_sums(cuda_api, dev, res=res, force_vec=vec)
 
 
 def test_strip_flux_and_momentum_exchange(cuda_api, dev):
