@@ -187,8 +187,19 @@ typedef struct jrl_step_desc
     const float *wall_phi;  /* phi_obs seen by the moving-wall step; NULL: same as phi_obs.
                                (demo_2d_LBM_cylinder.py:139-157 streams WITHOUT phi_obs -- plain halfway
                                bounce-back -- but passes phi_obs to solve_boundary) */
+    const uint8_t *tile_mask; /* NULL, or the packed summary of `flags` written by jrl_tile_mask_u8 for exactly
+                               these flags (same B, stored rows, W): lets the pipelined kernel skip the flag
+                               rows of all-FLUID tiles.  Results are identical with and without it; it must be
+                               recomputed whenever `flags` changes. */
 } jrl_step_desc;
 int jrl_step_f32(const jrl_step_desc *d, void *stream);
+
+/* Packed flag summary for jrl_step_desc.tile_mask: one byte per row segment of the library's tile width,
+ * 1 = every cell of the segment and its two x-neighbours (periodic) is FLUID.  Hs = stored rows (H, or
+ * slab_rows + 2).  jrl_tile_mask_bytes returns the size of `mask` in bytes (0 on bad arguments).
+ * Needs W % 16 == 0 and 16-byte aligned flags (the pipelined kernel's own requirements). */
+int jrl_tile_mask_bytes(int B, int Hs, int W);
+int jrl_tile_mask_u8(const uint8_t *flags, uint8_t *mask, int B, int Hs, int W, void *stream);
 
 /* ---- row-slab halo helpers (multi-GPU) ----------------------------------------------------------
  * Pack / unpack `nrows` full rows of all C planes of a [C,Hloc,W] slab starting at row `row`

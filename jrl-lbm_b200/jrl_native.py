@@ -43,7 +43,8 @@ class StepDesc(Structure):  # struct jrl_step_desc
                 ("vel", c_void_p), ("rho_out", c_void_p), ("vel_out", c_void_p), ("force", c_void_p),
                 ("mesh_grid", c_void_p), ("inflow_vel", c_void_p), ("inflow_density", c_double),
                 ("use_wall", c_int), ("obs_vel", c_void_p), ("slab_row0", c_int), ("slab_rows", c_int),
-                ("row_begin", c_int), ("row_end", c_int), ("force_vec", c_int), ("sums", c_void_p), ("wall_phi", c_void_p)]
+                ("row_begin", c_int), ("row_end", c_int), ("force_vec", c_int), ("sums", c_void_p), ("wall_phi", c_void_p),
+                ("tile_mask", c_void_p)]
 
 
 _vp, _i, _d, _f = c_void_p, c_int, c_double, c_float
@@ -65,6 +66,8 @@ PROTOTYPES = {
     "jrl_strip_flux_f32": [_vp, _vp, _i, _i, _vp, _i, _i, _vp],
     "jrl_momentum_exchange_f32": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "jrl_step_f32": [POINTER(StepDesc), _vp],
+    "jrl_tile_mask_bytes": [_i, _i, _i],
+    "jrl_tile_mask_u8": [_vp, _vp, _i, _i, _i, _vp],
     "jrl_halo_pack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "jrl_halo_unpack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
 }

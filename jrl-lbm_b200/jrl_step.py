@@ -55,6 +55,30 @@ class FusedStep:
                 self.contact_tan = math.tan(math.pi / 2.0 - float(ca))
         else:
             self.contact_tan = 0.0
+        self.use_tile_mask = True
+        self._masks = {}  # flags.data_ptr() -> (flags._version, shape, mask tensor)
+
+    def invalidate_masks(self):
+        """Forget the cached tile masks (needed only if a flags tensor was rewritten behind torch's back,
+        i.e. without bumping its version counter)."""
+        self._masks.clear()
+
+    def _tile_mask(self, flags, B, Hs, W):
+        """Packed all-FLUID summary of `flags` for the pipelined kernel (jrl_tile_mask_u8), recomputed
+        only when the tensor was written since the last call (torch's version counter)."""
+        key = flags.data_ptr()
+        hit = self._masks.get(key)
+        if hit is not None and hit[0] == flags._version and hit[1] == tuple(flags.shape):
+            return hit[2]
+        n = N.load().jrl_tile_mask_bytes(B, Hs, W)
+        if n <= 0:
+            return None
+        mask = hit[2] if hit is not None and hit[2].numel() == n else torch.empty((n,), dtype=torch.uint8, device=flags.device)
+        N.call("jrl_tile_mask_u8", ctypes.c_void_p(flags.data_ptr()), ctypes.c_void_p(mask.data_ptr()), B, Hs, W, like=flags)
+        if len(self._masks) >= 16:
+            self._masks.clear()
+        self._masks[key] = (flags._version, tuple(flags.shape), mask)
+        return mask
 
     def step(self, f, flags, rho=None, vel=None, *, f_out=None, rho_out=None, vel_out=None, store_moments=True,
              phi_obs=None, force=None, mesh_grid=None, inflow_vel=None, inflow_density=None, use_wall=False,
@@ -109,6 +133,11 @@ class FusedStep:
         d.force_vec = int(force_vec)
         d.sums = N.tensor_ptr(sums, "sums", torch.float64, (N.SUM_SLOTS, 4), like=f, optional=True)
         d.wall_phi = N.tensor_ptr(wall_phi, "wall_phi", shape=(B, 1, Hs, W), like=f, optional=True)
+        mask = None
+        if (self.use_tile_mask and W % 16 == 0 and W >= 512 and flags.data_ptr() % 16 == 0
+                and (force_vec == 8 or (force_vec == 0 and self.op == N.OP_BGK))):
+            mask = self._tile_mask(flags, B, Hs, W)
+        d.tile_mask = None if mask is None else mask.data_ptr()
         N.call("jrl_step_f32", ctypes.byref(d), like=f)
         if self.is_convection:
             return f_out, rho_out

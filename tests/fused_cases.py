@@ -50,3 +50,50 @@ def check_sums(api, device, res=(40, 64), force_vec=0):
     r, u = r.cpu().numpy().astype(np.float64), u.cpu().numpy().astype(np.float64)
     want = np.array([(r * fluid).sum(), (r * u[:, 0:1] * fluid).sum(), (r * u[:, 1:2] * fluid).sum(), fluid.sum()])
     assert np.allclose(tot, want, rtol=2e-6, atol=1e-6), (tot, want)
+
+
+def tile_mask_reference(flags, tw):
+    """numpy statement of jrl_tile_mask_u8: segment (row, c) is 1 iff every cell of [c*tw - 1, c*tw + cw]
+    (periodic in x) is FLUID."""
+    B, _, Hs, W = flags.shape
+    tpr = (W + tw - 1) // tw
+    fl = flags[:, 0] == 1
+    out = np.zeros((B, Hs, tpr), np.uint8)
+    for c in range(tpr):
+        x0, x1 = c * tw, min(W, (c + 1) * tw)
+        cols = [(x0 - 1) % W] + list(range(x0, x1)) + [x1 % W]
+        out[:, :, c] = fl[:, :, cols].all(axis=2)
+    return out
+
+
+def check_tile_mask(api, device, res=(9, 1040)):
+    assert res[0] >= 7
+    """jrl_tile_mask_u8 against the numpy statement, on mostly-FLUID flags with defects placed at segment
+    edges, row ends (periodic wrap) and in the partial last segment."""
+    import ctypes
+    import torch
+    import jrl_native as N
+    H, W = res
+    lib = N.load()
+    n = lib.jrl_tile_mask_bytes(2, H, W)
+    tpr = n // (2 * H)
+    tw = -(-W // tpr) if tpr > 1 else W
+    # recover the library's tile width from the segment count (W chosen so that it is not ambiguous)
+    for cand in (256, 512, 1024, 2048):
+        if -(-W // cand) == tpr:
+            tw = cand
+            break
+    flags = torch.ones((2, 1, H, W), dtype=torch.uint8)
+    flags[0, 0, 1, 0] = 2            # first cell: also the right neighbour of the last segment
+    flags[0, 0, 2, W - 1] = 8        # last cell: left neighbour of segment 0
+    flags[0, 0, 3, tw - 1] = 2       # last cell of segment 0 = left neighbour of segment 1
+    flags[0, 0, 4, tw] = 16          # first cell of segment 1 = right neighbour of segment 0
+    flags[1, 0, 5, W - 3] = 0        # inside the partial last segment
+    flags[1, 0, 6, tw // 2] = 32
+    flags = flags.to(device)
+    mask = torch.zeros((n,), dtype=torch.uint8, device=device)
+    N.call("jrl_tile_mask_u8", ctypes.c_void_p(flags.data_ptr()), ctypes.c_void_p(mask.data_ptr()), 2, H, W, like=flags)
+    got = mask.cpu().numpy().reshape(2, H, tpr)
+    want = tile_mask_reference(flags.cpu().numpy(), tw)
+    assert np.array_equal(got, want), (got, want)
+    assert want.sum() < want.size and want.sum() > 0

@@ -2,7 +2,7 @@
 import pytest
 import torch
 
-from fused_cases import FUSED_CASES, assert_identical, check_sums, run_pair
+from fused_cases import FUSED_CASES, assert_identical, check_sums, check_tile_mask, run_pair
 
 
 @pytest.mark.parametrize("name", list(FUSED_CASES))
@@ -13,3 +13,7 @@ def test_fused_equals_chain(emu_api, name):
 
 def test_step_sums(emu_api):
     check_sums(emu_api, torch.device("cpu"))
+
+
+def test_tile_mask(emu_api):
+    check_tile_mask(emu_api, torch.device("cpu"))

@@ -10,7 +10,7 @@ import pytest
 import torch
 
 import jrl_scenarios as S
-from fused_cases import FUSED_CASES, assert_identical, check_sums, run_pair
+from fused_cases import FUSED_CASES, assert_identical, check_sums, check_tile_mask, run_pair
 from golden_cases import CASES
 from util import compare_outputs, load_golden, rel_l2
 
@@ -109,6 +109,39 @@ def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym
     for o in outs[1:]:
         for a, b in zip(outs[0], o):
             assert np.array_equal(a, b, equal_nan=True)
+
+
+@pytest.mark.parametrize("res", [(9, 1040), (8, 4096), (7, 528)])
+def test_tile_mask(cuda_api, dev, res):
+    check_tile_mask(cuda_api, dev, res=res)
+
+
+def test_pipelined_kernel_with_and_without_tile_mask(cuda_api, dev):
+    """The tile mask only lets all-FLUID tiles skip their flag rows: populations, moments and in-kernel sums are
+    identical with it, without it, and after the flags change under a cached mask (version counter)."""
+    import jrl_step
+    H, W = 24, 4096
+    P = cuda_api.SimulationParameters(simulation_size=(1, 1, H, W), device=dev, tau=0.6, contact_angle=None)
+    st = S.random_state((H, W), 13, dev, obstacles=True, io_cells=True)
+    flags = torch.ones_like(st["flags"])
+    flags[:, :, 3:9, 700:1500] = st["flags"][:, :, 3:9, 700:1500]     # a patch of obstacles / inlets in a FLUID sea
+    fs = jrl_step.FusedStep(P, operator="bgk")
+    kw = dict(phi_obs=st["phi"], inflow_density=0.5, force=st["force"], inflow_vel=torch.tensor([0.01, 0.02], device=dev))
+
+    def run(use_mask, fl):
+        fs.use_tile_mask = use_mask
+        return [t.cpu().numpy() for t in fs.step(st["f"], fl, st["rho"], st["vel"], force_vec=8, **kw)]
+    a, b = run(True, flags), run(False, flags)
+    assert fs._masks, "the mask was not built"
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y, equal_nan=True)
+    flags[:, :, 15, 2000:2100] = 2                                      # in-place edit: version counter moves
+    a, b = run(True, flags), run(False, flags)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y, equal_nan=True)
+    ref = [t.cpu().numpy() for t in fs.step(st["f"], flags, st["rho"], st["vel"], force_vec=4, **kw)]
+    for x, y in zip(a, ref):
+        assert np.array_equal(x, y, equal_nan=True)
 
 
 @pytest.mark.parametrize("res,vec", [((40, 64), 0), ((21, 19), 0), ((24, 2048), 8), ((24, 2048), 4), ((24, 1040), 8)])

@@ -6,7 +6,7 @@ sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200")); sys.path.insert(0, ROOT)
 import torch
 import jrl_native
 
-def run(lib, G=8192, steps=20, op="bgk"):
+def run(lib, G=int(os.environ.get("G", 8192)), steps=20, op="bgk"):
     jrl_native._lib = None
     jrl_native.LIB_PATH = lib
     jrl_native.load()
@@ -38,4 +38,7 @@ if __name__ == "__main__":
     ops = os.environ.get("OPS", "bgk").split(",")
     for lib in sys.argv[1:]:
         for op in ops:
-            print(os.path.basename(lib), op, "GB/s:", json.dumps(run(os.path.abspath(lib), op=op)), flush=True)
+            try:
+                print(os.path.basename(lib), op, "GB/s:", json.dumps(run(os.path.abspath(lib), op=op)), flush=True)
+            except Exception as e:
+                print(os.path.basename(lib), op, "FAILED:", str(e)[:120], flush=True)
