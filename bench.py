@@ -384,9 +384,9 @@ def main():
     except Exception:
         pass
     achieved = BYTES_PER_LUP * G * G / world / (ms_per_step * 1e-3) / 1e9   # per GPU: its cells / the step time
-    roofline = {"bound": "hbm", "kernel": "jrl::pipe::k_step_pipe<OP_BGK, 0, 4, 2, 2> (jrl_step_f32)", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "jrl::pipe::k_step_pipe<OP_BGK, 0, 4, 2, 2> (jrl_step_f32; 512-cell tiles, TMA ring, producer warp)", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": traffic,
-                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum per lattice update at 8192^2 (profiles/r1_traffic.json) x cells of this launch",
+                "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per lattice update at 8192^2 (profiles/r1_traffic.json) x cells of this launch",
                 "algorithmic_bytes_per_launch": BYTES_PER_LUP * G * G / world,
                 "note": "per GPU; 72 B per lattice update x cells per rank / CUDA-event step time (1 dominant launch per step)"}
     line = {"metric": METRIC, "value": mlups, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
@@ -394,7 +394,9 @@ def main():
             "data": "synthetic",
             "config": {"workload": f"demo_2d_LBM.py double shear layer, D2Q9 BGK, periodic, {G}x{G} fp32 (BASELINE configs[4] strong-scaling grid)",
                        "grid": G, "tau": shear_tau(G), "rows_per_rank": wl.nrows, "decomposition": "row slabs, ring halo exchange (NCCL)" if world > 1 else "single domain",
-                       "moments_stored_every": OUT_EVERY, "l2": "working set (2 x %.1f GB of populations per rank) is far larger than the 126 MB L2" % (36.0 * G * G / world / 1e9)},
+                       "moments_stored_every": OUT_EVERY,
+                       "flags": "static all-FLUID field; its packed tile mask (jrl_tile_mask_u8) is built once in the value leg and rebuilt every step in the e2e leg (flags re-uploaded)",
+                       "l2": "working set (2 x %.1f GB of populations per rank) is far larger than the 126 MB L2" % (36.0 * G * G / world / 1e9)},
             "roofline": roofline, "e2e": e2e, "gpu_launches": int(nl.item()), "mass_drift": mass_rel}
     if rank == 0:
         line["clocks"] = clocks.summary()

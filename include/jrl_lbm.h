@@ -194,6 +194,19 @@ typedef struct jrl_step_desc
 } jrl_step_desc;
 int jrl_step_f32(const jrl_step_desc *d, void *stream);
 
+/* Multi-step driver: `nsteps` lattice updates with the descriptor's buffers used as ping-pong pairs --
+ * the time loop of the reference's demos (demo_2d_LBM.py:101-119, demo_2d_LBM_cylinder.py:138-172)
+ * below the ABI, for grids small enough to be paced by the host.  Step i reads (f_in, rho, vel) and writes
+ * (f_out, rho_out, vel_out), then the pairs swap: after the call the newest populations are in f_out when
+ * nsteps is odd and in f_in when it is even; likewise rho / rho_out and vel / vel_out when BOTH members
+ * of a pair are given (then they are state: OBSTACLE cells keep their previous moments, INFLOW cells and
+ * the moving wall read them).  When rho or vel is NULL the moments are pure outputs, written to rho_out /
+ * vel_out every `store_every`-th step (0: never) and at the last step.  In the concentration form vel is
+ * the advecting velocity (an input, never swapped).  sums (optional): step i adds into sums + i *
+ * sums_stride doubles (stride 0: one accumulator; JRL_SUM_SLOTS * 4: a per-step series).  Inputs that the
+ * reference's demos rewrite every step (flags, phi_obs, ...) stay fixed for the whole call. */
+int jrl_run_f32(const jrl_step_desc *d, int nsteps, int store_every, long long sums_stride, void *stream);
+
 /* Packed flag summary for jrl_step_desc.tile_mask: one byte per row segment of the library's tile width,
  * 1 = every cell of the segment and its two x-neighbours (periodic) is FLUID.  Hs = stored rows (H, or
  * slab_rows + 2).  jrl_tile_mask_bytes returns the size of `mask` in bytes (0 on bad arguments).

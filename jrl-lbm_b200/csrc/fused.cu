@@ -665,11 +665,13 @@ __device__ __noinline__ float4 step_group_generic(const StepArgs &a, int b, int 
 // pull their cells into registers, arrive on `empty` (one arrival per warp) and then do the arithmetic
 // and the stores -- so a stage is refilled while its previous contents are still being computed on,
 // and no warp ever waits for another consumer warp.
-// registers per thread that let MINB CTAs of `threads` threads share the 64 K-entry register file
-// (registers are allocated to warp pairs)
+// Registers per thread that let MINB CTAs of `threads` threads be resident: each of the SM's four
+// sub-partitions has 16 K registers and takes every fourth warp.  (ptxas' own choice under
+// __launch_bounds__(threads, MINB) is more conservative and spills.)
 constexpr int pipe_maxreg(int threads, int minb)
 {
-    const int r = 65536 / (minb * ((threads + 63) / 64) * 64) / 8 * 8;
+    const int warps = minb * ((threads + 31) / 32);
+    const int r = 16384 / (32 * ((warps + 3) / 4)) / 8 * 8;
     return r > 255 ? 255 : r;
 }
 
@@ -707,6 +709,9 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
                 const unsigned long long tj = (unsigned long long)t + (unsigned long long)lane * gridDim.x;
                 const bool u = tj < total && tile_uniform(a, tile_of(a, (unsigned)tj, tpr, rows));
                 ubits = __ballot_sync(0xffffffffu, u);
+#ifdef JRL_EXP_ALL_UNIFORM
+                ubits = 0xffffffffu;
+#endif
             }
             if (lane == 0)
             {
@@ -731,7 +736,11 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
         // ---- shared memory -> registers (everything this thread needs from the stage) ---------------
         float tv[9][VEC], edge[9];
         uint32_t w[3] = {0u, 0u, 0u}, el[3] = {0u, 0u, 0u}, er[3] = {0u, 0u, 0u};
+#ifdef JRL_EXP_CONSUMER_UNIFORM
+        const bool uniform = true;
+#else
         const bool uniform = st.uniform != 0u;  // CTA-uniform
+#endif
         if (active)
         {
 #pragma unroll
@@ -821,7 +830,10 @@ static int launch_cfg(const StepArgs &a, unsigned total, unsigned tpr, unsigned 
 template <int OP, int CONV>
 static int launch_one(const StepArgs &a, unsigned total, unsigned tpr, unsigned rows, cudaStream_t s)
 {
-    return launch_cfg<OP, CONV, 4, JRL_PIPE_STAGES, JRL_PIPE_MINB>(a, total, tpr, rows, s);
+#ifndef JRL_PIPE_VEC
+#define JRL_PIPE_VEC 4
+#endif
+    return launch_cfg<OP, CONV, JRL_PIPE_VEC, JRL_PIPE_STAGES, JRL_PIPE_MINB>(a, total, tpr, rows, s);
 }
 
 static bool eligible(const StepArgs &a, int B)
@@ -976,7 +988,7 @@ extern "C" int jrl_tile_mask_u8(const uint8_t *flags, uint8_t *mask, int B, int 
     return check_launch(fn);
 }
 
-extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream)
+static int step_once(const jrl_step_desc *d, void *stream)
 {
     const char *fn = "jrl_step_f32";
     JRL_REQUIRE(d, fn, "null descriptor");
@@ -1089,4 +1101,53 @@ extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream)
         JRL_LAUNCH(k_contact_ring, dim3(blocks_for(ring, 128), d->B), 128, s, a.g, d->rho, d->flags, d->rho_out, d->contact_tan);
     }
     return check_launch(fn);
+}
+
+extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream) { return step_once(d, stream); }
+
+// Multi-step driver: the time loop of the reference's demos (demo_2d_LBM.py:101-119 and siblings) moved
+// below the C ABI, so that small, launch-bound grids are not paced by the Python interpreter.
+extern "C" int jrl_run_f32(const jrl_step_desc *d0, int nsteps, int store_every, long long sums_stride, void *stream)
+{
+    const char *fn = "jrl_run_f32";
+    JRL_REQUIRE(d0, fn, "null descriptor");
+    JRL_REQUIRE(nsteps >= 0, fn, "nsteps must be >= 0");
+    JRL_REQUIRE(sums_stride >= 0, fn, "sums_stride must be >= 0");
+    jrl_step_desc d = *d0;
+    // previous-step moments are state (OBSTACLE cells keep them, INFLOW cells and the moving wall read
+    // them) whenever both buffers of a pair are given: they ping-pong with the populations
+    const bool pp_rho = d.rho != nullptr && d.rho_out != nullptr;
+    const bool pp_vel = !d.is_convection && d.vel != nullptr && d.vel_out != nullptr;
+    float *const rho_last = d.rho_out, *const vel_last = d.vel_out;
+    for (int i = 0; i < nsteps; ++i)
+    {
+        if (!pp_rho && !pp_vel)
+        {
+            // moments are pure outputs: store them every `store_every`-th step and at the last step
+            const bool store = i == nsteps - 1 || (store_every > 0 && (i + 1) % store_every == 0);
+            d.rho_out = store ? rho_last : nullptr;
+            d.vel_out = store ? vel_last : nullptr;
+        }
+        const int rc = step_once(&d, stream);
+        if (rc != 0)
+            return rc;
+        const float *fi = d.f_in;
+        d.f_in = d.f_out;
+        d.f_out = const_cast<float *>(fi);
+        if (pp_rho)
+        {
+            float *t = d.rho;
+            d.rho = d.rho_out;
+            d.rho_out = t;
+        }
+        if (pp_vel)
+        {
+            float *t = d.vel;
+            d.vel = d.vel_out;
+            d.vel_out = t;
+        }
+        if (d.sums)
+            d.sums += sums_stride;
+    }
+    return JRL_OK;
 }

@@ -66,6 +66,7 @@ PROTOTYPES = {
     "jrl_strip_flux_f32": [_vp, _vp, _i, _i, _vp, _i, _i, _vp],
     "jrl_momentum_exchange_f32": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "jrl_step_f32": [POINTER(StepDesc), _vp],
+    "jrl_run_f32": [POINTER(StepDesc), _i, _i, ctypes.c_longlong, _vp],
     "jrl_tile_mask_bytes": [_i, _i, _i],
     "jrl_tile_mask_u8": [_vp, _vp, _i, _i, _i, _vp],
     "jrl_halo_pack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],

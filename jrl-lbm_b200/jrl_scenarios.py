@@ -87,6 +87,15 @@ def shear_layer(api, device, res=(130, 130), steps=1000, operator="bgk", kbc_typ
     out = {"tau": tau, "f0": _np(f)}
     if fused:  # extension of this repo: the same loop body as ONE launch per step (jrl_step.FusedStep)
         fs = R.create_fused_step(operator=operator, kbc_type=kbc_type if operator == "kbc" else None, dx=dx, dt=dt)
+    if fused == "run":  # the whole loop below the C ABI (jrl_run_f32), cut only where a snapshot is wanted
+        done = 0
+        for stop in sorted(set(int(x) for x in snapshots if 0 < int(x) < steps)) + [steps]:
+            f, density, vel = fs.run(f, flags, density, vel, stop - done, force=force)
+            done = stop
+            if done in snapshots:
+                out[f"snap_{done}_rho"] = _np(density)
+                out[f"snap_{done}_vel"] = _np(vel)
+        steps = 0
     for step in range(steps):
         if fused:
             f, density, vel = fs.step(f, flags, density, vel, force=force)
@@ -153,6 +162,16 @@ def cylinder(api, device, res=(800, 400), D=20, steps=2000, Re=5000.0, Vmax=0.05
     out = {"tau": tau, "flags": _np(flags), "phi_obs": _np(phi_obs)}
     if fused:
         fs = R.create_fused_step(operator="mrt", dx=dx, dt=dt)
+    if fused == "run":
+        done = 0
+        for stop in sorted(set(int(x) for x in snapshots if 0 < int(x) < steps)) + [steps]:
+            f, density, vel = fs.run(f, flags, density, vel, stop - done, force=force, inflow_density=1.0,
+                                     inflow_vel=inflow_vel, use_wall=True, wall_phi=phi_obs, obs_vel=phi_obs_vel)
+            done = stop
+            if done in snapshots:
+                out[f"snap_{done}_rho"] = _np(density)
+                out[f"snap_{done}_vel"] = _np(vel)
+        steps = 0
     for step in range(steps):
         if fused:
             f, density, vel = fs.step(f, flags, density, vel, force=force, inflow_density=1.0, inflow_vel=inflow_vel,

@@ -92,6 +92,18 @@ class FusedStep:
         rows = (begin, end): update only these global rows;
         sums: float64 [SUM_SLOTS, 4] device tensor this launch adds {sum rho, sum rho ux, sum rho uy,
         cells} to (see new_sums / total_sums)."""
+        d, f_out, rho_out, vel_out, _keep = self._desc(f, flags, rho, vel, f_out, rho_out, vel_out, store_moments, phi_obs,
+                                                       force, mesh_grid, inflow_vel, inflow_density, use_wall, obs_vel,
+                                                       wall_phi, clamp01, slab, rows, force_vec, sums)
+        N.call("jrl_step_f32", ctypes.byref(d), like=f)
+        if self.is_convection:
+            return f_out, rho_out
+        return f_out, rho_out, vel_out
+
+    def _desc(self, f, flags, rho, vel, f_out, rho_out, vel_out, store_moments, phi_obs, force, mesh_grid, inflow_vel,
+              inflow_density, use_wall, obs_vel, wall_phi, clamp01, slab, rows, force_vec, sums, sums_shape=None):
+        """Validated jrl_step_desc for these tensors (+ the output tensors it allocated and the objects that
+        must stay alive until the launch has been issued)."""
         B, Hs, W = _dims(f)
         H = Hs
         d = N.StepDesc()
@@ -131,17 +143,44 @@ class FusedStep:
         d.use_wall = int(bool(use_wall))
         d.obs_vel = N.tensor_ptr(obs_vel, "obs_vel", shape=(B, 2, Hs, W), like=f, optional=True)
         d.force_vec = int(force_vec)
-        d.sums = N.tensor_ptr(sums, "sums", torch.float64, (N.SUM_SLOTS, 4), like=f, optional=True)
+        d.sums = N.tensor_ptr(sums, "sums", torch.float64, sums_shape or (N.SUM_SLOTS, 4), like=f, optional=True)
         d.wall_phi = N.tensor_ptr(wall_phi, "wall_phi", shape=(B, 1, Hs, W), like=f, optional=True)
         mask = None
         if (self.use_tile_mask and W % 16 == 0 and W >= 512 and flags.data_ptr() % 16 == 0
                 and (force_vec == 8 or (force_vec == 0 and self.op == N.OP_BGK))):
             mask = self._tile_mask(flags, B, Hs, W)
         d.tile_mask = None if mask is None else mask.data_ptr()
-        N.call("jrl_step_f32", ctypes.byref(d), like=f)
+        return d, f_out, rho_out, vel_out, (force, mask)
+
+    def run(self, f, flags, rho=None, vel=None, nsteps=1, *, f_alt=None, rho_alt=None, vel_alt=None, store_every=0,
+            phi_obs=None, force=None, mesh_grid=None, inflow_vel=None, inflow_density=None, use_wall=False, obs_vel=None,
+            wall_phi=None, clamp01=False, force_vec=0, sums=None):
+        """`nsteps` lattice updates in ONE library call (jrl_run_f32): the demo's time loop below the C ABI, for
+        grids small enough to be paced by the interpreter.  The per-step inputs (flags, phi_obs, force, ...) stay
+        fixed for the whole call.  f_alt / rho_alt / vel_alt: the second buffer of each ping-pong pair (allocated
+        when not given).  When `rho` / `vel` are given they are state and ping-pong with the populations; when
+        None the moments are outputs stored every `store_every`-th step and at the last one.
+        sums: None, a [SUM_SLOTS, 4] accumulator, or a [nsteps, SUM_SLOTS, 4] per-step series (float64).
+        Returns the newest (f, rho, vel) -- (h, C) in the concentration form."""
+        nsteps = int(nsteps)
+        if f_alt is None:
+            f_alt = torch.empty_like(f)
+        series = sums is not None and sums.dim() == 3
+        d, f_alt, rho_alt, vel_alt, _keep = self._desc(
+            f, flags, rho, vel, f_alt, rho_alt, vel_alt, True, phi_obs, force, mesh_grid, inflow_vel, inflow_density,
+            use_wall, obs_vel, wall_phi, clamp01, None, None, force_vec, sums,
+            sums_shape=(nsteps, N.SUM_SLOTS, 4) if series else None)
+        N.call("jrl_run_f32", ctypes.byref(d), nsteps, int(store_every), N.SUM_SLOTS * 4 if series else 0, like=f)
+        N.launch_count += max(0, nsteps - 1)
+        odd = nsteps % 2 == 1
+        f_new = f_alt if odd else f
+        state_rho = rho is not None
+        state_vel = vel is not None and not self.is_convection
+        rho_new = (rho_alt if odd else rho) if state_rho else rho_alt
         if self.is_convection:
-            return f_out, rho_out
-        return f_out, rho_out, vel_out
+            return f_new, rho_new
+        vel_new = (vel_alt if odd else vel) if state_vel else vel_alt
+        return f_new, rho_new, vel_new
 
 
 def new_sums(device):

@@ -97,3 +97,41 @@ def check_tile_mask(api, device, res=(9, 1040)):
     want = tile_mask_reference(flags.cpu().numpy(), tw)
     assert np.array_equal(got, want), (got, want)
     assert want.sum() < want.size and want.sum() > 0
+
+
+RUN_CASES = {
+    "shear_bgk": ("shear_layer", dict(res=(40, 32), steps=25, operator="bgk", snapshots=(10,))),
+    "shear_mrt": ("shear_layer", dict(res=(24, 32), steps=20, operator="mrt", kbc_type=133)),
+    "shear_kbc_a": ("shear_layer", dict(res=(24, 24), steps=9, operator="kbc", kbc_type=133)),
+    "cylinder": ("cylinder", dict(res=(64, 48), D=8, steps=41, center=(24.0, 22.0), snapshots=(20,))),
+}
+
+
+def check_run_equals_steps(api, device, name):
+    """jrl_run_f32 (the time loop below the ABI) == one jrl_step_f32 per step, bit for bit."""
+    fn, kw = RUN_CASES[name]
+    stepped = getattr(S, fn)(api, device, fused=True, **kw)
+    ran = getattr(S, fn)(api, device, fused="run", **kw)
+    assert_identical(stepped, ran)
+
+
+def check_run_sums_series(api, device):
+    """Per-step sums series of FusedStep.run == the sums of single steps; moments-as-outputs mode."""
+    import torch
+    import jrl_native as N
+    import jrl_step
+    H, W = 24, 32
+    P = api.SimulationParameters(simulation_size=(1, 1, H, W), device=device, tau=0.7, contact_angle=None)
+    fs = jrl_step.FusedStep(P, operator="bgk")
+    rho, vel = S.shear_layer_state((H, W), device)
+    f0 = api.SimulationRunner(P).create_collision().get_feq_(dx=1.0, dt=1.0, rho=rho, vel=vel)
+    flags = torch.ones((1, 1, H, W), dtype=torch.uint8, device=device)
+    n = 7
+    series = torch.zeros((n, N.SUM_SLOTS, 4), dtype=torch.float64, device=device)
+    f_run, r_run, v_run = fs.run(f0.clone(), flags, None, None, n, sums=series)
+    f = f0.clone()
+    for i in range(n):
+        one = jrl_step.new_sums(device)
+        f, r, v = fs.step(f, flags, None, None, sums=one)
+        assert torch.allclose(series[i].sum(0), one.sum(0), rtol=1e-12, atol=0)
+    assert torch.equal(f_run, f) and torch.equal(r_run, r) and torch.equal(v_run, v)

@@ -2,7 +2,8 @@
 import pytest
 import torch
 
-from fused_cases import FUSED_CASES, assert_identical, check_sums, check_tile_mask, run_pair
+from fused_cases import (FUSED_CASES, RUN_CASES, assert_identical, check_run_equals_steps, check_run_sums_series,
+                         check_sums, check_tile_mask, run_pair)
 
 
 @pytest.mark.parametrize("name", list(FUSED_CASES))
@@ -17,3 +18,12 @@ def test_step_sums(emu_api):
 
 def test_tile_mask(emu_api):
     check_tile_mask(emu_api, torch.device("cpu"))
+
+
+@pytest.mark.parametrize("name", list(RUN_CASES))
+def test_run_equals_steps(emu_api, name):
+    check_run_equals_steps(emu_api, torch.device("cpu"), name)
+
+
+def test_run_sums_series(emu_api):
+    check_run_sums_series(emu_api, torch.device("cpu"))

@@ -10,7 +10,8 @@ import pytest
 import torch
 
 import jrl_scenarios as S
-from fused_cases import FUSED_CASES, assert_identical, check_sums, check_tile_mask, run_pair
+from fused_cases import (FUSED_CASES, RUN_CASES, assert_identical, check_run_equals_steps, check_run_sums_series,
+                         check_sums, check_tile_mask, run_pair)
 from golden_cases import CASES
 from util import compare_outputs, load_golden, rel_l2
 
@@ -109,6 +110,15 @@ def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym
     for o in outs[1:]:
         for a, b in zip(outs[0], o):
             assert np.array_equal(a, b, equal_nan=True)
+
+
+@pytest.mark.parametrize("name", list(RUN_CASES))
+def test_run_equals_steps(cuda_api, dev, name):
+    check_run_equals_steps(cuda_api, dev, name)
+
+
+def test_run_sums_series(cuda_api, dev):
+    check_run_sums_series(cuda_api, dev)
 
 
 @pytest.mark.parametrize("res", [(9, 1040), (8, 4096), (7, 528)])

@@ -67,12 +67,15 @@ def native_cases(S, api, dev):
         ("c4_conc_walk", "jrl_conc", dict(res=(128, 64), balance_steps=0), "walk_steps", 128 * 64, (100, 600), True),
         ("c5_fluid_stageA", "jrl_fluid", dict(res=(128, 64), gravity_strength=2e-5), "steps", 128 * 64, (100, 600), False),
     ]
+    label = {False: "solver-object chain + demo host work", True: "fused step (1 launch per step from Python) + demo host work",
+             "run": "jrl_run_f32: the whole time loop in one library call"}
     for name, fn, kw, key, cells, (n1, n2), has_fused in cases:
-        for fused in ((False, True) if has_fused else (False,)):
-            k2 = dict(kw, fused=True) if fused else kw
-            us = scenario_us_per_step(S, api, dev, fn, k2, key, n1, n2)
-            emit(config=name, variant="fused step (1 launch) + demo host work" if fused else "solver-object chain + demo host work",
-                 grid=list(kw["res"]), us_per_step=round(us, 2), mlups=round(cells / us, 1))
+        modes = (False,) if not has_fused else ((False, True) if fn == "jrl_conc" else (False, True, "run"))
+        for fused in modes:
+            k2 = dict(kw, fused=fused) if fused else kw
+            m1, m2 = (n1 * 10, n2 * 10) if fused == "run" else (n1, n2)
+            us = scenario_us_per_step(S, api, dev, fn, k2, key, m1, m2)
+            emit(config=name, variant=label[fused], grid=list(kw["res"]), us_per_step=round(us, 2), mlups=round(cells / us, 1))
 
 
 def big_cases(S, api, dev, G):
