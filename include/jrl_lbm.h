@@ -214,6 +214,53 @@ int jrl_run_f32(const jrl_step_desc *d, int nsteps, int store_every, long long s
 int jrl_tile_mask_bytes(int B, int Hs, int W);
 int jrl_tile_mask_u8(const uint8_t *flags, uint8_t *mask, int B, int Hs, int W, void *stream);
 
+/* ---- device-side tip motion ----------------------------------------------------
+ * One launch replaces the per-step host work of the JRL concentration demos' walk loop
+ * (demo_2d_LBM_JRL_C_cylinder.py:283-307): signed distance of the moving tip (CalculateObsPhi_forC, :31-41),
+ * flags restamp (top row when not is_negative, OBSTACLE where phi < 0, the INFLOW strip on the tip face),
+ * C = 0 in OBSTACLE cells, and the advecting velocity C_vel = (vel0 * w0 + vel1 * w1) * vel_obs_conv with the
+ * tip interior stamped to (0, vel_obs_conv).  vel1 == NULL: C_vel = vel0 * vel_obs_conv.  Batch size 1.
+ * flags and C are updated in place; phi_obs [1,1,H,W] and C_vel [1,2,H,W] are fully written.  The scalars
+ * are what the demo's python holds at that step: box_cx / box_cy = the fp32 box_center tensor, walks_int =
+ * int(walks + 0.5 dx), w0 = (float)(1 - t), w1 = (float)t. */
+typedef struct jrl_tip_desc
+{
+    int H, W;
+    int is_negative;
+    int walks_int, Rg_radius, radius_obs_int;
+    float box_cx, box_cy, box_radius;
+    float vel_obs_conv, w0, w1;
+    const float *mesh_grid; /* [1,2,H,W] cell centres */
+    uint8_t *flags;         /* [1,1,H,W] in/out */
+    float *C;               /* [1,1,H,W] in/out */
+    const float *vel0;      /* [2,H,W] velocity snapshot, normalised by the tip speed */
+    const float *vel1;      /* [2,H,W] next snapshot, or NULL */
+    float *phi_obs;         /* [1,1,H,W] out */
+    float *C_vel;           /* [1,2,H,W] out */
+} jrl_tip_desc;
+int jrl_tip_prepare_conc_f32(const jrl_tip_desc *d, void *stream);
+
+/* Stage-B walk loop below the ABI (SURVEY 8f ranks 1 + 2; demo_2d_LBM_JRL_C_cylinder.py:281-362): per step
+ * jrl_tip_prepare_conc_f32 -> [jrl_tile_mask_u8 when step.tile_mask is set] -> jrl_step_f32 (concentration
+ * form) -> two strip fluxes -> walks += vel_obs_conv * dt.  `step`: f_in / f_out = the h ping-pong pair,
+ * rho / rho_out = the C pair, vel = the C_vel buffer, phi_obs = the phi buffer (both rewritten every step),
+ * flags (rewritten in place), mesh_grid, inflow_density, clamp01 as for jrl_step_f32.  `tip`: the static
+ * fields (H, W, is_negative, Rg_radius, radius_obs_int, box_cx, box_radius, vel_obs_conv, mesh_grid); the
+ * per-step ones are filled here.  vel_snaps [n_snaps,2,H,W]: velocity snapshots at tip travel 0,
+ * x_interval, ... interpolated as the demo does (:294-303).  records [nsteps][4] (device) = {inflow flux,
+ * inflow strip sum, current flux, current strip sum} per step.  After the call the newest h / C are in
+ * f_out / rho_out when nsteps is odd, in f_in / rho when even, and `walks` holds the new tip position. */
+typedef struct jrl_walk_desc
+{
+    jrl_step_desc step;
+    jrl_tip_desc tip;
+    double walks, vel_obs_conv, dx, dt, box_radius, inflow_height, x_interval;
+    const float *vel_snaps;
+    int n_snaps;
+    float *records;
+} jrl_walk_desc;
+int jrl_conc_walk_f32(jrl_walk_desc *w, int nsteps, void *stream);
+
 /* ---- row-slab halo helpers (multi-GPU) ----------------------------------------------------------
  * Pack / unpack `nrows` full rows of all C planes of a [C,Hloc,W] slab starting at row `row`
  * into a contiguous [C,nrows,W] staging buffer (the message NCCL sends to the neighbour rank). */

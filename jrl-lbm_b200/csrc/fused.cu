@@ -148,8 +148,11 @@ __device__ __forceinline__ void step_generic(const StepArgs &a, const Grid &g, l
 // ---- moments + collision + stores of one group whose post-stream populations are in fc ----------------
 template <int VEC, int OP, int CONV>
 __device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, long long b, int y, int x0, long long r0,
-                                            float fc[VEC][9], const uint8_t me[VEC], bool active, float acc[3])
+                                            float fc[VEC][9], const uint8_t me[VEC], bool active, float acc[3],
+                                            const float (*pre)[VEC] = nullptr)
 {
+    // pre (concentration form, pipelined kernel): this group's advecting velocity [0], [1] and mesh_grid row
+    // [2] (x for CONV 1, y for CONV 2), fetched one tile ahead so that their latency is off the critical path
     const float *rho = a.rho ? a.rho + b * g.HW : nullptr;
     const float *vel = a.vel ? a.vel + b * 2 * g.HW : nullptr;
     float r_out[VEC], ux_out[VEC], uy_out[VEC];
@@ -171,8 +174,8 @@ __device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, lo
             r = obs ? (rho ? rho[self] : 0.f) : sum9(fc[k]);
             if (a.clamp01)
                 r = fminf(fmaxf(r, 0.f), 1.f);
-            ux = vel ? vel[self] : 0.f;
-            uy = vel ? vel[g.HW + self] : 0.f;
+            ux = pre ? pre[0][k] : (vel ? vel[self] : 0.f);
+            uy = pre ? pre[1][k] : (vel ? vel[g.HW + self] : 0.f);
         }
         else if (obs)
         {
@@ -207,9 +210,9 @@ __device__ __forceinline__ void step_finish(const StepArgs &a, const Grid &g, lo
             }
             float rr = 1.f;
             if (CONV == 1)
-                rr = a.mesh[b * 2 * g.HW + self];
+                rr = pre ? pre[2][k] : a.mesh[b * 2 * g.HW + self];
             else if (CONV == 2)
-                rr = y == 0 ? 1.f : a.mesh[b * 2 * g.HW + g.HW + self] - a.half_dx;
+                rr = y == 0 ? 1.f : (pre ? pre[2][k] : a.mesh[b * 2 * g.HW + g.HW + self]) - a.half_dx;
             collide_cell<OP, CONV>(a.cp, r, ux, uy, a.force != nullptr, fx, fy, rr, nullptr, fc[k]);
         }
     }
@@ -494,38 +497,47 @@ __global__ void __launch_bounds__(kThreads, JRL_STEP_MIN_BLOCKS) k_step(const __
 
 #ifndef JRL_HOST_EMU
 // =====================================================================================================
-// Pipelined variant for wide grids: persistent CTAs, TMA bulk copies (cp.async.bulk, SASS UBLKCP) into a
-// 2-stage shared-memory ring, completion on an mbarrier.
+// Pipelined variant for wide grids: persistent, warp-specialised CTAs; TMA bulk copies (cp.async.bulk,
+// SASS UBLKCP) into a shared-memory ring behind full / empty mbarrier pairs.
 //
 // Why: the register-prefetch kernel above keeps only (resident threads x 144 B) of loads in flight and
-// none while a thread is in its collision arithmetic; at 2 CTAs/SM it tops out near 4 TB/s while a plain
-// copy with the same access pattern reaches 6.7 TB/s (tools/membench.cu, profiles/README.md).  Here one
-// elected thread issues the NEXT tile's loads (9 direction rows + 3 flag rows, ~41 KB) as soon as the
-// stage's previous contents have been pulled into registers, so every CTA always has 1-2 tiles in
-// flight regardless of what its warps are doing: bytes in flight per SM are set by shared memory
-// (2 CTAs x 2 stages x 41 KB), not by registers or occupancy.
+// none while a thread is in its collision arithmetic (4.0-4.5 TB/s).  Here a producer warp issues the
+// next tile's copies (9 direction rows, + 3 flag rows unless the tile mask says the neighbourhood is all
+// FLUID, + velocity / mesh rows in the concentration form) as soon as the consumer warps have pulled the
+// stage's previous contents into registers, so loads are in flight regardless of what the consumers do.
+// About 74 KB in flight per SM is the optimum (2 CTAs x 2 stages x 18.6 KB): more loads in flight starve
+// the stores (tools/tmabench.cu).
 //
-// Tile = one row segment of CW = 1024 cells (256 threads x 4 cells).  Direction q's buffer holds
+// Tile = one row segment of CW = 512 cells (128 consumer threads x 4 cells).  Direction q's buffer holds
 // f[q][y - e_qy][x0 - 4 .. x0 + cw + 4) so that the pull f[q](x - e_qx) is a shared-memory read at
 // offset -e_qx; the 4-float halos wrap periodically at the row ends (separate 16-byte copies there).
 // Groups whose 3 x 6 neighbourhood is not all FLUID (or that sit on a symmetry axis) ignore the staged
-// data and take step_generic(), exactly like k_step: both kernels produce identical bits.
-// Requirements (checked by the launcher): W % 16 == 0, W >= JRL_PIPE_CW, 16-byte aligned f_in / flags.
+// data and take the out-of-line generic path, built from the same device functions as k_step: both
+// kernels produce identical bits.
+// Requirements (checked by the launcher): W % 16 == 0, W >= JRL_PIPE_CW, 16-byte aligned planes.
 // =====================================================================================================
 namespace pipe {
 
 constexpr int CW = JRL_PIPE_CW, HALO = 4, ROWF = CW + 2 * HALO, FHALO = 16, ROWB = CW + 2 * FHALO;
 
+constexpr unsigned kPoison = 0xffffffffu;  // Stage::tile value that tells the consumers there is no more work
+
+// NEX: extra staged rows (concentration form: advecting velocity x, y and the mesh row)
+template <int NEX>
 struct Stage
 {
     alignas(16) float f[9][ROWF];
+    alignas(16) float ex[NEX > 0 ? NEX : 1][NEX > 0 ? CW : 4];
     alignas(16) uint8_t fl[3][ROWB];
     alignas(8) unsigned long long full;   // mbarrier: tile landed (1 arrival + transaction bytes)
     unsigned long long empty;             // mbarrier: every consumer warp has pulled this fill into registers
     unsigned int uniform;                 // this fill: 3 x (cw + 2) neighbourhood all FLUID (tile mask) -> fl[] not loaded
-    unsigned int pad[3];
+    unsigned int tile;                    // this fill's tile index, or kPoison
+    unsigned int pad[2];
 };
-static_assert(sizeof(Stage) % 16 == 0, "stage stride must keep 16-byte alignment");
+static_assert(sizeof(Stage<0>) % 16 == 0 && sizeof(Stage<3>) % 16 == 0, "stage stride must keep 16-byte alignment");
+__host__ __device__ constexpr int conv_rows(int conv) { return conv == 0 ? 0 : (conv == 3 ? 2 : 3); }
+
 
 __device__ __forceinline__ uint32_t s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(void *bar, uint32_t count)
@@ -593,7 +605,8 @@ __device__ __forceinline__ bool tile_uniform(const StepArgs &a, const Tile &tl)
 
 // one thread: arm the barrier and issue every bulk copy of tile `tl` into `st`; `uniform`: the tile mask
 // says the whole neighbourhood is FLUID, so the flag rows are neither copied nor looked at
-__device__ __forceinline__ void issue_tile(const StepArgs &a, const Tile &tl, Stage &st, bool uniform)
+template <int CONV>
+__device__ __forceinline__ void issue_tile(const StepArgs &a, const Tile &tl, Stage<conv_rows(CONV)> &st, bool uniform)
 {
     const Grid &g = a.g;
     const int W = g.W, y = tl.y, x0 = tl.x0, cw = tl.cw;
@@ -603,7 +616,19 @@ __device__ __forceinline__ void issue_tile(const StepArgs &a, const Tile &tl, St
     const bool b_in = x0 >= FHALO && x0 + cw + FHALO <= W;
     const uint32_t fbytes = (uint32_t)(cw + 2 * HALO) * 4u, bbytes = (uint32_t)(cw + 2 * FHALO);
     st.uniform = uniform ? 1u : 0u;  // ordered before the consumers' reads by the arrive (release) below
-    mbar_expect_tx(&st.full, 9u * fbytes - 3u * 2u * HALO * 4u + (uniform ? 0u : 3u * bbytes));  // the 3 e_qx == 0 directions carry no halo
+    mbar_expect_tx(&st.full, 9u * fbytes - 3u * 2u * HALO * 4u + (uniform ? 0u : 3u * bbytes) +
+                                 (uint32_t)conv_rows(CONV) * (uint32_t)cw * 4u);  // the 3 e_qx == 0 directions carry no halo
+    if (CONV != 0)
+    {
+        // concentration form: this row segment of the advecting velocity (and of the mesh coordinate the
+        // symmetry axis needs) rides along with the populations
+        const float *v = a.vel + (long long)tl.b * 2 * g.HW + row[1] + x0;
+        bulk_g2s(&st.ex[0][0], v, (uint32_t)cw * 4u, &st.full);
+        bulk_g2s(&st.ex[1][0], v + g.HW, (uint32_t)cw * 4u, &st.full);
+        if (CONV == 1 || CONV == 2)
+            bulk_g2s(&st.ex[2][0], a.mesh + (long long)tl.b * 2 * g.HW + (CONV == 2 ? g.HW : 0) + row[1] + x0, (uint32_t)cw * 4u,
+                     &st.full);
+    }
     const float *f = a.f_in + (long long)tl.b * 9 * g.HW;
     const uint8_t *fl = a.flags + (long long)tl.b * g.HW;
     const int xl = x0 == 0 ? W - HALO : x0 - HALO, xr = x0 + cw == W ? 0 : x0 + cw;
@@ -680,8 +705,9 @@ __global__ void __launch_bounds__(CW / VEC + 32) __maxnreg__(pipe_maxreg(CW / VE
 k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, unsigned rows)
 {
     constexpr int kCons = CW / VEC;
+    using StageT = Stage<conv_rows(CONV)>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Stage *stages = reinterpret_cast<Stage *>(smem_raw);
+    StageT *stages = reinterpret_cast<StageT *>(smem_raw);
     const Grid &g = a.g;
     const int tid = threadIdx.x;
     if (tid == 0)
@@ -698,8 +724,11 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
     if (tid >= kCons)
     {
         // ---- producer warp ------------------------------------------------------------------------
-        // Every 32 tiles all lanes look up the tile mask of this CTA's next 32 tiles at once (one DRAM /
-        // L2 round trip per batch, off lane 0's critical path); lane 0 alone waits and issues.
+        // Static round-robin (tile blockIdx.x + k gridDim.x): at any moment the CTAs work on neighbouring
+        // 2 KB chunks of every plane, which is what the DRAM likes -- a dynamic scheduler handing out 1, 2, 4
+        // or 8 consecutive tiles per atomicAdd measured 4.9 / 5.7 / 4.3 / 4.5 TB/s against 5.9 TB/s for this.
+        // Every 32 tiles all lanes look up the tile mask of this CTA's next 32 tiles at once (one L2 / DRAM
+        // round trip per batch, off lane 0's critical path); lane 0 alone waits for a free stage and issues.
         const unsigned lane = (unsigned)(tid - kCons);
         unsigned it = 0, ubits = 0u;
         for (unsigned t = blockIdx.x; t < total; t += gridDim.x, ++it)
@@ -709,38 +738,49 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
                 const unsigned long long tj = (unsigned long long)t + (unsigned long long)lane * gridDim.x;
                 const bool u = tj < total && tile_uniform(a, tile_of(a, (unsigned)tj, tpr, rows));
                 ubits = __ballot_sync(0xffffffffu, u);
-#ifdef JRL_EXP_ALL_UNIFORM
-                ubits = 0xffffffffu;
-#endif
             }
             if (lane == 0)
             {
-                Stage &st = stages[it % STAGES];
+                StageT &st = stages[it % STAGES];
                 if (it >= (unsigned)STAGES)
                     mbar_wait(&st.empty, ((it / STAGES) - 1u) & 1u);
-                issue_tile(a, tile_of(a, t, tpr, rows), st, ((ubits >> (it & 31u)) & 1u) != 0u);
+                st.tile = t;
+                issue_tile<CONV>(a, tile_of(a, t, tpr, rows), st, ((ubits >> (it & 31u)) & 1u) != 0u);
             }
             __syncwarp();
+        }
+        if (lane == 0)
+        {
+            // no more work: complete the next stage's `full` phase with a poison tile
+            StageT &st = stages[it % STAGES];
+            if (it >= (unsigned)STAGES)
+                mbar_wait(&st.empty, ((it / STAGES) - 1u) & 1u);
+            st.tile = kPoison;
+            mbar_arrive(&st.full);
         }
         return;
     }
     // ---- consumer warps -------------------------------------------------------------------------------
-    unsigned it = 0;
-    for (unsigned t = blockIdx.x; t < total; t += gridDim.x, ++it)
+    for (unsigned it = 0;; ++it)
     {
-        Stage &st = stages[it % STAGES];
+        StageT &st = stages[it % STAGES];
+        mbar_wait(&st.full, (it / STAGES) & 1u);
+        const unsigned t = st.tile;
+        if (t == kPoison)
+            break;
         const Tile tl = tile_of(a, t, tpr, rows);
         const int x0 = tl.x0 + VEC * tid, y = tl.y;
         const bool active = VEC * tid < tl.cw;
-        mbar_wait(&st.full, (it / STAGES) & 1u);
         // ---- shared memory -> registers (everything this thread needs from the stage) ---------------
         float tv[9][VEC], edge[9];
+        float cur[3][VEC];
         uint32_t w[3] = {0u, 0u, 0u}, el[3] = {0u, 0u, 0u}, er[3] = {0u, 0u, 0u};
-#ifdef JRL_EXP_CONSUMER_UNIFORM
-        const bool uniform = true;
-#else
         const bool uniform = st.uniform != 0u;  // CTA-uniform
-#endif
+        // Group on the x symmetry axis: its negative-x neighbour is the cell itself and the three links that
+        // cross the axis pull the x-mirrored population (propagation.cu:74-87, 135-143) -- which sits in the
+        // same stage, same row, column 0 of the mirrored direction's buffer.  Handled here so that one group
+        // per ROW does not fall to the generic path (19 us each; 4x the whole step on the scaled C4 grid).
+        const bool axis_x = g.axisym == AXI_X && x0 == 0;
         if (active)
         {
 #pragma unroll
@@ -749,8 +789,11 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
                 const float *row = &st.f[q][HALO + VEC * tid];
                 VecIO<VEC>::load(row, tv[q]);
                 const int ex = JRL_EX(q);
-                edge[q] = ex > 0 ? row[-1] : (ex < 0 ? row[VEC] : 0.f);
+                edge[q] = ex > 0 ? (axis_x ? st.f[mirror_x(q)][HALO] : row[-1]) : (ex < 0 ? row[VEC] : 0.f);
             }
+#pragma unroll
+            for (int j = 0; j < conv_rows(CONV); ++j)
+                VecIO<VEC>::load(&st.ex[j][VEC * tid], cur[j]);
             if (!uniform)
 #pragma unroll
             for (int r = 0; r < 3; ++r)
@@ -769,11 +812,11 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
         if (active)
         {
             // ---- classify (rows: 0 = y-1, 1 = y, 2 = y+1) ---------------------------------------------
-            bool bulk = !(g.axisym == AXI_X && x0 == 0) && !(g.axisym == AXI_Y && y == 0);
+            bool bulk = !(g.axisym == AXI_Y && y == 0);
             const uint32_t fluid_word = VEC == 4 ? 0x01010101u : 0x0101u;
 #pragma unroll
             for (int r = 0; r < 3; ++r)
-                bulk = bulk && w[r] == fluid_word && el[r] == CT_FLUID && er[r] == CT_FLUID;
+                bulk = bulk && w[r] == fluid_word && (axis_x || el[r] == CT_FLUID) && er[r] == CT_FLUID;
             if (bulk || uniform)
             {
                 float fc[VEC][9];
@@ -790,7 +833,7 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
 #pragma unroll
                 for (int k = 0; k < VEC; ++k)
                     me[k] = CT_FLUID;
-                step_finish<VEC, OP, CONV>(a, g, tl.b, y, x0, cell(g, y, y, 0), fc, me, true, acc);
+                step_finish<VEC, OP, CONV>(a, g, tl.b, y, x0, cell(g, y, y, 0), fc, me, true, acc, CONV != 0 ? cur : nullptr);
                 cells = (float)VEC;
             }
             else
@@ -811,7 +854,7 @@ template <int OP, int CONV, int VEC, int STAGES, int MINB>
 static int launch_cfg(const StepArgs &a, unsigned total, unsigned tpr, unsigned rows, cudaStream_t s)
 {
     auto kern = k_step_pipe<OP, CONV, VEC, STAGES, MINB>;
-    const size_t smem = sizeof(Stage) * STAGES;
+    const size_t smem = sizeof(Stage<conv_rows(CONV)>) * STAGES;
     static bool configured = false;  // per instantiation
     if (!configured)
     {
@@ -819,7 +862,13 @@ static int launch_cfg(const StepArgs &a, unsigned total, unsigned tpr, unsigned 
             return JRL_ERR_CUDA;
         configured = true;
     }
-    const unsigned nb = min(total, (unsigned)(MINB * sm_count()));
+    // CTA b works on tiles b, b + nb, b + 2 nb, ...: with nb coprime to the tiles per row every CTA visits every
+    // tile column equally often, so a boundary that costs extra in one column (a side wall, an inlet, the
+    // symmetry axis) is shared by all CTAs instead of landing on the nb / gcd(nb, tpr) ones that own that column.
+    unsigned nb = min(total, (unsigned)(MINB * sm_count()));
+    auto gcd = [](unsigned x, unsigned y) { while (y) { const unsigned r = x % y; x = y; y = r; } return x; };
+    while (nb > 1 && gcd(nb, tpr) != 1)
+        --nb;
     kern<<<nb, CW / VEC + 32, smem, s>>>(a, total, tpr, rows);
     return 0;
 }
@@ -844,6 +893,8 @@ static bool eligible(const StepArgs &a, int B)
     if (((uintptr_t)a.f_in | (uintptr_t)a.flags | (uintptr_t)a.f_out) % 16 != 0)
         return false;
     if ((a.rho_out && (uintptr_t)a.rho_out % 16 != 0) || (a.vel_out && (uintptr_t)a.vel_out % 16 != 0))
+        return false;
+    if (a.cp.convection && (((uintptr_t)a.vel | (uintptr_t)a.mesh) % 16 != 0))  // prefetched as 128-bit vectors
         return false;
     const long long tiles = (long long)B * (a.row_end - a.row_begin) * ((g.W + CW - 1) / CW);
     return tiles < (1ll << 31);
@@ -1069,10 +1120,13 @@ static int step_once(const jrl_step_desc *d, void *stream)
 #ifndef JRL_HOST_EMU
     // automatic choice: the pipelined kernel wins for BGK (memory-bound); MRT / KBC are bound by their
     // arithmetic and run faster in the register kernel (3.8 vs 3.1 TB/s MRT at 8192^2)
-    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4 && d->op == JRL_OP_BGK))
+    // (the concentration form on real geometries -- tip block, inlet column, symmetry axis -- has too many groups
+    // on the generic path for the pipelined kernel's eight consumer warps per SM: 3.4 ms vs 1.9 ms per step on
+    // the scaled C4 grid, so it also defaults to the register kernel; force_vec = 8 selects the pipeline)
+    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4 && d->op == JRL_OP_BGK && !d->is_convection))
     {
         const bool ok = vec == 4 && pipe::eligible(a, d->B);
-        JRL_REQUIRE(ok || d->force_vec == 0, fn, "pipelined kernel needs W % 16 == 0, W >= 1024 and 16-byte aligned planes");
+        JRL_REQUIRE(ok || d->force_vec == 0, fn, "pipelined kernel needs W % 16 == 0, W >= 512 and 16-byte aligned planes");
         if (ok)
         {
             const int prc = pipe::launch(a, d->B, s);
@@ -1154,5 +1208,86 @@ extern "C" int jrl_run_f32(const jrl_step_desc *d0, int nsteps, int store_every,
         if (d.sums)
             d.sums += sums_stride;
     }
+    return JRL_OK;
+}
+
+// Stage-B walk loop of the JRL concentration demos below the C ABI (SURVEY 8f ranks 1 + 2):
+// per step  tip motion (1 launch) -> [tile mask] -> fused concentration step (1 launch) -> the two strip
+// fluxes the demo records (2 launches) -> walks += vel_obs_conv dt, with every host scalar evaluated as the
+// demo's python evaluates it (demo_2d_LBM_JRL_C_cylinder.py:281-362).
+extern "C" int jrl_conc_walk_f32(jrl_walk_desc *w, int nsteps, void *stream)
+{
+    const char *fn = "jrl_conc_walk_f32";
+    JRL_REQUIRE(w, fn, "null descriptor");
+    JRL_REQUIRE(nsteps >= 0, fn, "nsteps must be >= 0");
+    JRL_REQUIRE(w->vel_snaps && w->n_snaps >= 1 && w->x_interval > 0.0, fn, "velocity snapshots required");
+    JRL_REQUIRE(w->records, fn, "records required");
+    jrl_step_desc d = w->step;
+    jrl_tip_desc t = w->tip;
+    JRL_REQUIRE(d.is_convection && d.B == 1 && d.rho && d.rho_out && d.vel && d.phi_obs && d.mesh_grid, fn,
+                "step descriptor: concentration form, B = 1, C ping-pong pair, C_vel, phi_obs and mesh_grid buffers required");
+    JRL_REQUIRE(d.slab_rows == 0, fn, "single-domain only");
+    const long long HW = (long long)d.H * d.W;
+    double walks = w->walks;
+    for (int i = 0; i < nsteps; ++i)
+    {
+        // -- host scalars, as the demo computes them (:283-284, :294-303)
+        const int walks_int = (int)(walks + 0.5 * w->dx);
+        JRL_REQUIRE(walks_int >= 1 && walks_int + 1 < d.H, fn, "the tip left the grid");
+        t.walks_int = walks_int;
+        t.box_cy = (float)(walks - w->box_radius);
+        const double x_comp = walks - w->inflow_height;
+        int b = (int)(x_comp / w->x_interval);
+        if (b > w->n_snaps - 1)
+            b = w->n_snaps - 1;
+        if (b < 0)
+            b = 0;
+        t.vel0 = w->vel_snaps + (long long)b * 2 * HW;
+        if (b + 1 < w->n_snaps)
+        {
+            const double tw = x_comp / w->x_interval - b;
+            t.vel1 = t.vel0 + 2 * HW;
+            t.w0 = (float)(1.0 - tw);
+            t.w1 = (float)tw;
+        }
+        else
+        {
+            t.vel1 = nullptr;
+            t.w0 = 1.f;
+            t.w1 = 0.f;
+        }
+        t.flags = const_cast<uint8_t *>(d.flags);
+        t.C = d.rho;
+        t.phi_obs = const_cast<float *>(d.phi_obs);
+        t.C_vel = d.vel;
+        int rc = jrl_tip_prepare_conc_f32(&t, stream);
+        if (rc != 0)
+            return rc;
+        if (d.tile_mask)
+        {
+            rc = jrl_tile_mask_u8(d.flags, const_cast<uint8_t *>(d.tile_mask), 1, d.H, d.W, stream);
+            if (rc != 0)
+                return rc;
+        }
+        rc = step_once(&d, stream);
+        if (rc != 0)
+            return rc;
+        // -- records on the new C (:344-362): inflow strip at walks_int, current strip at walks_int + 1
+        float *rec = w->records + 4ll * i;
+        rc = jrl_strip_flux_f32(d.rho_out, d.mesh_grid, walks_int, t.radius_obs_int, rec, d.H, d.W, stream);
+        if (rc != 0)
+            return rc;
+        rc = jrl_strip_flux_f32(d.rho_out, d.mesh_grid, walks_int + 1, t.radius_obs_int, rec + 2, d.H, d.W, stream);
+        if (rc != 0)
+            return rc;
+        const float *fi = d.f_in;
+        d.f_in = d.f_out;
+        d.f_out = const_cast<float *>(fi);
+        float *c = d.rho;
+        d.rho = d.rho_out;
+        d.rho_out = c;
+        walks += w->vel_obs_conv * w->dt;
+    }
+    w->walks = walks;
     return JRL_OK;
 }

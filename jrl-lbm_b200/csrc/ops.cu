@@ -315,13 +315,12 @@ __global__ void __launch_bounds__(kThreads) k_wall(Grid g, WallParams p, const f
         o[q * g.HW] = fc[q];
 }
 
-#ifndef JRL_HOST_EMU  // warp-shuffle kernels: GPU only
 // ---- R8: strip reductions, one warp, shuffle tree --------------------------------------------------
-__global__ void k_strip_flux(const float *__restrict__ C, const float *__restrict__ mesh, int y0, int ncol, int W,
-                             float *__restrict__ out2)
+__device__ __forceinline__ void strip_terms(const float *__restrict__ C, const float *__restrict__ mesh, int y0, int ncol, int W,
+                                            int k, float &flux, float &plain)
 {
-    const int k = threadIdx.x;
-    float flux = 0.f, plain = 0.f;
+    flux = 0.f;
+    plain = 0.f;
     for (int c = k; c < ncol; c += 32)
     {
         // area_k = pi (k+1)^2 - pi k^2 in fp32 (demo_2d_LBM_JRL_C_cylinder.py:176-180)
@@ -334,6 +333,28 @@ __global__ void k_strip_flux(const float *__restrict__ C, const float *__restric
         flux += (dz + dr) * area;
         plain += c0 * area;
     }
+}
+
+__global__ void k_strip_flux(const float *__restrict__ C, const float *__restrict__ mesh, int y0, int ncol, int W,
+                             float *__restrict__ out2)
+{
+#ifdef JRL_HOST_EMU
+    // one host "thread" plays the 32 lanes and the same xor tree, so the bits equal the GPU's
+    float fl[32], pl[32];
+    for (int k = 0; k < 32; ++k)
+        strip_terms(C, mesh, y0, ncol, W, k, fl[k], pl[k]);
+    for (int off = 16; off > 0; off >>= 1)
+        for (int k = 0; k < off; ++k)
+        {
+            fl[k] += fl[k + off];
+            pl[k] += pl[k + off];
+        }
+    out2[0] = fl[0];
+    out2[1] = pl[0];
+#else
+    const int k = threadIdx.x;
+    float flux, plain;
+    strip_terms(C, mesh, y0, ncol, W, k, flux, plain);
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1)
     {
@@ -345,8 +366,10 @@ __global__ void k_strip_flux(const float *__restrict__ C, const float *__restric
         out2[0] = flux;
         out2[1] = plain;
     }
+#endif
 }
 
+#ifndef JRL_HOST_EMU  // warp-shuffle kernels: GPU only
 // ---- R9 (extension): momentum exchange over halfway bounce-back links -------------------------------
 __global__ void __launch_bounds__(kThreads) k_momentum_exchange(Grid g, const float *__restrict__ f,
                                                                 const uint8_t *__restrict__ flags, double *out2)
@@ -408,6 +431,56 @@ __global__ void __launch_bounds__(kThreads) k_momentum_exchange(Grid g, const fl
 }
 
 #endif  // !JRL_HOST_EMU
+
+// ---- device-side tip motion: the per-step input preparation of the JRL concentration
+//      demos -- ~15 host-driven torch ops per step (demo_2d_LBM_JRL_C_cylinder.py:283-307) -- in one launch.
+//      Arithmetic follows the torch expressions operation for operation (fp32 tensors, python scalars cast
+//      to fp32), so the fields equal the demo's bit for bit.
+__global__ void __launch_bounds__(kThreads) k_tip_conc(jrl_tip_desc d)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long HW = (long long)d.H * d.W;
+    if (i >= HW)
+        return;
+    const int y = (int)(i / d.W), x = (int)(i - (long long)y * d.W);
+    const float mx = d.mesh_grid[i], my = d.mesh_grid[HW + i];
+    // CalculateObsPhi_forC (:31-41): box signed distance in the max norm, united (min) with the top wall
+    const float tx = (mx - d.box_cx) - d.box_radius;
+    const float ty = (my - d.box_cy) - d.box_radius;
+    float phi = tx > ty ? tx : ty;
+    if (d.is_negative)
+    {
+        const float top = -(my - (float)d.H);
+        phi = phi < top ? phi : top;
+    }
+    uint8_t fl = d.flags[i];
+    if (!d.is_negative && y == d.H - 1)
+        fl = CT_INFLOW_2;                                   // :287-289
+    if (phi < 0.f)
+        fl = CT_OBSTACLE;                                   // :290
+    if (y == d.walks_int - 1 && x < d.radius_obs_int)
+        fl = CT_INFLOW;                                     // :291
+    d.flags[i] = fl;
+    if (fl == CT_OBSTACLE)
+        d.C[i] = 0.f;                                       // :292
+    d.phi_obs[i] = phi;
+    // :294-307  vel = v[b] * (1 - t) + v[b + 1] * t  (or v[b]);  C_vel = vel / 1 * vel_obs_conv; tip interior stamped
+    float vx = d.vel0[i], vy = d.vel0[HW + i];
+    if (d.vel1)
+    {
+        vx = vx * d.w0 + d.vel1[i] * d.w1;
+        vy = vy * d.w0 + d.vel1[HW + i] * d.w1;
+    }
+    vx = vx * d.vel_obs_conv;
+    vy = vy * d.vel_obs_conv;
+    if (y < d.walks_int && x < d.Rg_radius)
+    {
+        vx = 0.f;
+        vy = d.vel_obs_conv;
+    }
+    d.C_vel[i] = vx;
+    d.C_vel[HW + i] = vy;
+}
 
 // ---- halo staging ----------------------------------------------------------------------------------
 __global__ void k_halo_copy(float *__restrict__ dst, const float *__restrict__ src, int C, long long plane_dst,
@@ -667,11 +740,11 @@ int jrl_strip_flux_f32(const float *C, const float *mesh_grid, int y0, int ncol,
     JRL_REQUIRE(C && mesh_grid && out2, fn, "null pointer");
     JRL_REQUIRE(y0 >= 1 && y0 < H && ncol >= 1 && ncol + 1 <= W, fn, "strip outside the grid");
 #ifdef JRL_HOST_EMU
-    return fail_arg(fn, "warp-shuffle kernel: not part of the host emulation build");
+    JRL_LAUNCH(k_strip_flux, 1, 1, (cudaStream_t)stream, C, mesh_grid, y0, ncol, W, out2);
 #else
     JRL_LAUNCH(k_strip_flux, 1, 32, (cudaStream_t)stream, C, mesh_grid, y0, ncol, W, out2);
-    return check_launch(fn);
 #endif
+    return check_launch(fn);
 }
 
 int jrl_momentum_exchange_f32(const float *f_post, const uint8_t *flags, double *out2, int B, int H, int W, void *stream)
@@ -686,6 +759,18 @@ int jrl_momentum_exchange_f32(const float *f_post, const uint8_t *flags, double 
     JRL_LAUNCH(k_momentum_exchange, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, f_post, flags, out2);
     return check_launch(fn);
 #endif
+}
+
+int jrl_tip_prepare_conc_f32(const jrl_tip_desc *d, void *stream)
+{
+    const char *fn = "jrl_tip_prepare_conc_f32";
+    JRL_REQUIRE(d, fn, "null descriptor");
+    JRL_REQUIRE(d->H >= 3 && d->W >= 3, fn, "H, W >= 3 required");
+    JRL_REQUIRE(d->mesh_grid && d->flags && d->C && d->vel0 && d->phi_obs && d->C_vel, fn,
+                "mesh_grid, flags, C, vel0, phi_obs, C_vel required");
+    JRL_REQUIRE(d->C_vel != d->vel0 && d->C_vel != d->vel1, fn, "C_vel must not alias the velocity snapshots");
+    JRL_LAUNCH(k_tip_conc, blocks_for((long long)d->H * d->W), kThreads, (cudaStream_t)stream, *d);
+    return check_launch(fn);
 }
 
 int jrl_halo_pack_f32(const float *field, float *staging, int C, int Hloc, int W, int row, int nrows, void *stream)

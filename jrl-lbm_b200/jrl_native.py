@@ -47,6 +47,19 @@ class StepDesc(Structure):  # struct jrl_step_desc
                 ("tile_mask", c_void_p)]
 
 
+class TipDesc(Structure):  # struct jrl_tip_desc
+    _fields_ = [("H", c_int), ("W", c_int), ("is_negative", c_int), ("walks_int", c_int), ("Rg_radius", c_int),
+                ("radius_obs_int", c_int), ("box_cx", c_float), ("box_cy", c_float), ("box_radius", c_float),
+                ("vel_obs_conv", c_float), ("w0", c_float), ("w1", c_float), ("mesh_grid", c_void_p), ("flags", c_void_p),
+                ("C", c_void_p), ("vel0", c_void_p), ("vel1", c_void_p), ("phi_obs", c_void_p), ("C_vel", c_void_p)]
+
+
+class WalkDesc(Structure):  # struct jrl_walk_desc
+    _fields_ = [("step", StepDesc), ("tip", TipDesc), ("walks", c_double), ("vel_obs_conv", c_double), ("dx", c_double),
+                ("dt", c_double), ("box_radius", c_double), ("inflow_height", c_double), ("x_interval", c_double),
+                ("vel_snaps", c_void_p), ("n_snaps", c_int), ("records", c_void_p)]
+
+
 _vp, _i, _d, _f = c_void_p, c_int, c_double, c_float
 # name -> argtypes; every symbol include/jrl_lbm.h declares (tests/test_abi.py checks the list against the header)
 PROTOTYPES = {
@@ -69,6 +82,8 @@ PROTOTYPES = {
     "jrl_run_f32": [POINTER(StepDesc), _i, _i, ctypes.c_longlong, _vp],
     "jrl_tile_mask_bytes": [_i, _i, _i],
     "jrl_tile_mask_u8": [_vp, _vp, _i, _i, _i, _vp],
+    "jrl_tip_prepare_conc_f32": [POINTER(TipDesc), _vp],
+    "jrl_conc_walk_f32": [POINTER(WalkDesc), _i, _vp],
     "jrl_halo_pack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "jrl_halo_unpack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
 }

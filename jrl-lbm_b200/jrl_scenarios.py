@@ -297,10 +297,13 @@ def analytic_tip_velocity(mesh_grid, walks, r0):
 
 def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0.34013, radius_obs=6.50000000000001,
              inflow_height=20.50000000000001, Rg=4, vel_obs_conv=None, is_negative=True, clamp=True,
-             dx=1, dt=1, vel_field=None, fused=False):
+             dx=1, dt=1, vel_field=None, fused=False, vel_snaps=None, x_interval=0.1, device_tip=False):
     """Stage B.  `vel_field`: callable(mesh_grid, walks) -> normalised [1,2,H,W] velocity
     (defaults to `analytic_tip_velocity`); the demo interpolates HDF5 snapshots instead
-    (:294-303).  Returns final C, h and the per-step inflow/current flux series (:344-362)."""
+    (:294-303).  `vel_snaps` [n,2,H,W]: velocity snapshots at tip travel 0, x_interval, 2 x_interval, ...
+    interpolated per step exactly as the demo does (:294-303); `device_tip`: the walk loop's host work
+    (phi, flags, C reset, C_vel) as ONE launch (jrl_solver.tip_prepare_conc) instead of torch ops; needs
+    vel_snaps.  Returns final C, h and the per-step inflow/current flux series (:344-362)."""
     dtype = torch.float32
     c = dx / dt
     cs2 = c * c / 3.0
@@ -363,18 +366,48 @@ def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0
     if vel_field is None:
         vel_field = lambda mg, w: analytic_tip_velocity(mg, w, radius_obs)  # noqa: E731
     inflow, current = [], []
+    if device_tip == "run":  # the whole walk loop below the C ABI (jrl_conc_walk_f32)
+        import jrl_step
+        h, C, rec, walks, phi_obs, C_vel = jrl_step.conc_walk(
+            fs, h, C_flags, C, mesh_grid, vel_snaps, walks, walk_steps, box_center_x=float(box_center[0]), box_radius=box_radius,
+            Rg_radius=Rg_radius, radius_obs_int=radius_obs_int, vel_obs_conv=vel_obs_conv, inflow_height=inflow_height,
+            x_interval=x_interval, is_negative=is_negative, clamp01=clamp, dx=dx, dt=dt)
+        inflow, current = list(rec[:, 0]), list(rec[:, 2])
+        for _ in range(walk_steps):
+            R.step()
+        walk_steps = 0
+    if device_tip:
+        import jrl_solver
+        phi_buf, vel_buf = torch.empty_like(C), torch.empty_like(C_vel)
     for step in range(walk_steps):                                        # :281-407
         walks_int = int(walks + 0.5 * dx)
         box_center[1] = walks - box_radius
-        phi_obs = tip_phi(api, mesh_grid, box_center, box_radius, is_negative)
-        if not is_negative:
-            C_flags[..., -1, :] = int(CT.INFLOW_2)
-        C_flags[phi_obs < 0] = int(CT.OBSTACLE)
-        C_flags[..., walks_int - 1, 0:radius_obs_int] = int(CT.INFLOW)
-        C[C_flags == int(CT.OBSTACLE)] = 0.0
-        C_vel = vel_field(mesh_grid, walks) * vel_obs_conv
-        C_vel[:, 0, 0:walks_int, 0:Rg_radius] = 0
-        C_vel[:, 1, 0:walks_int, 0:Rg_radius] = vel_obs_conv
+        if vel_snaps is not None:                                         # :294-303
+            x_comp = walks - inflow_height
+            batch_idx = min(int(x_comp / x_interval), vel_snaps.shape[0] - 1)
+            t_w = x_comp / x_interval - batch_idx if batch_idx + 1 < vel_snaps.shape[0] else None
+        if device_tip:
+            phi_obs, C_vel = jrl_solver.tip_prepare_conc(
+                mesh_grid, C_flags, C, vel_snaps[batch_idx], None if t_w is None else vel_snaps[batch_idx + 1],
+                0.0 if t_w is None else t_w, box_center, box_radius, walks_int, Rg_radius, radius_obs_int, vel_obs_conv,
+                is_negative=is_negative, phi_out=phi_buf, vel_out=vel_buf)
+        else:
+            phi_obs = tip_phi(api, mesh_grid, box_center, box_radius, is_negative)
+            if not is_negative:
+                C_flags[..., -1, :] = int(CT.INFLOW_2)
+            C_flags[phi_obs < 0] = int(CT.OBSTACLE)
+            C_flags[..., walks_int - 1, 0:radius_obs_int] = int(CT.INFLOW)
+            C[C_flags == int(CT.OBSTACLE)] = 0.0
+            if vel_snaps is not None:
+                if t_w is not None:
+                    vel_now = vel_snaps[batch_idx] * (1 - t_w) + vel_snaps[batch_idx + 1] * t_w
+                else:
+                    vel_now = vel_snaps[batch_idx]
+                C_vel = vel_now.unsqueeze(0) / 1 * vel_obs_conv
+            else:
+                C_vel = vel_field(mesh_grid, walks) * vel_obs_conv
+            C_vel[:, 0, 0:walks_int, 0:Rg_radius] = 0
+            C_vel[:, 1, 0:walks_int, 0:Rg_radius] = vel_obs_conv
         if fused:
             h, C = fs.step(h, C_flags, C, C_vel.contiguous(), phi_obs=phi_obs, mesh_grid=mesh_grid, inflow_density=0,
                            clamp01=clamp)

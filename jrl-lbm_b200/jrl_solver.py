@@ -403,3 +403,41 @@ def momentum_exchange(f_post, flags):
            N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f_post),
            ctypes.c_void_p(out.data_ptr()), B, H, W, like=f_post)
     return out
+
+
+def tip_prepare_conc(mesh_grid, flags, C, vel0, vel1, t, box_center, box_radius, walks_int, Rg_radius, radius_obs_int,
+                     vel_obs_conv, is_negative=True, phi_out=None, vel_out=None):
+    """Device-side tip motion for the JRL concentration walk loop (jrl_tip_prepare_conc_f32): one launch instead
+    of the demo's ~15 torch ops per step (demo_2d_LBM_JRL_C_cylinder.py:283-307).  flags and C are updated in
+    place; returns (phi_obs, C_vel).  vel0 / vel1: [2,H,W] (or [1,2,H,W]) velocity snapshots and the interpolation
+    weight t (vel1 None: vel0 alone); box_center: the demo's fp32 [2] tensor or a pair of floats."""
+    B, H, W = _dims(C, "C")
+    if B != 1:
+        raise RuntimeError("tip_prepare_conc: batch size 1 only")
+    d = N.TipDesc()
+    d.H, d.W, d.is_negative = H, W, int(bool(is_negative))
+    d.walks_int, d.Rg_radius, d.radius_obs_int = int(walks_int), int(Rg_radius), int(radius_obs_int)
+    bc = box_center.detach().to("cpu", torch.float32).tolist() if isinstance(box_center, torch.Tensor) else list(box_center)
+    d.box_cx, d.box_cy, d.box_radius = float(bc[0]), float(bc[1]), float(box_radius)
+    d.vel_obs_conv = float(vel_obs_conv)
+    d.w0, d.w1 = float(1.0 - t), float(t)
+    d.mesh_grid = N.tensor_ptr(mesh_grid, "mesh_grid", shape=(1, 2, H, W), like=C)
+    d.flags = N.tensor_ptr(flags, "flags", torch.uint8, (1, 1, H, W), like=C)
+    d.C = N.tensor_ptr(C, "C", shape=(1, 1, H, W))
+    v0 = vel0.reshape(1, 2, H, W)
+    d.vel0 = N.tensor_ptr(v0, "vel0", shape=(1, 2, H, W), like=C)
+    v1 = None if vel1 is None else vel1.reshape(1, 2, H, W)
+    d.vel1 = N.tensor_ptr(v1, "vel1", shape=(1, 2, H, W), like=C, optional=True)
+    if phi_out is None:
+        phi_out = torch.empty_like(C)
+    if vel_out is None:
+        vel_out = torch.empty((1, 2, H, W), dtype=C.dtype, device=C.device)
+    d.phi_obs = N.tensor_ptr(phi_out, "phi_obs", shape=(1, 1, H, W), like=C)
+    d.C_vel = N.tensor_ptr(vel_out, "C_vel", shape=(1, 2, H, W), like=C)
+    N.call("jrl_tip_prepare_conc_f32", ctypes.byref(d), like=C)
+    # the kernel wrote flags behind torch's back: bump the version counter so that cached tile masks are rebuilt
+    try:
+        torch.autograd.graph.increment_version(flags)
+    except AttributeError:
+        flags.add_(0)
+    return phi_out, vel_out

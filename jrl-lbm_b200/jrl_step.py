@@ -147,7 +147,7 @@ class FusedStep:
         d.wall_phi = N.tensor_ptr(wall_phi, "wall_phi", shape=(B, 1, Hs, W), like=f, optional=True)
         mask = None
         if (self.use_tile_mask and W % 16 == 0 and W >= 512 and flags.data_ptr() % 16 == 0
-                and (force_vec == 8 or (force_vec == 0 and self.op == N.OP_BGK))):
+                and (force_vec == 8 or (force_vec == 0 and self.op == N.OP_BGK and not self.is_convection))):
             mask = self._tile_mask(flags, B, Hs, W)
         d.tile_mask = None if mask is None else mask.data_ptr()
         return d, f_out, rho_out, vel_out, (force, mask)
@@ -181,6 +181,47 @@ class FusedStep:
             return f_new, rho_new
         vel_new = (vel_alt if odd else vel) if state_vel else vel_alt
         return f_new, rho_new, vel_new
+
+
+def conc_walk(fs, h, flags, C, mesh_grid, vel_snaps, walks, nsteps, *, box_center_x, box_radius, Rg_radius, radius_obs_int,
+              vel_obs_conv, inflow_height, x_interval=0.1, is_negative=True, clamp01=True, dx=1.0, dt=1.0, records=None):
+    """`nsteps` of the JRL concentration demos' walk loop in ONE library call (jrl_conc_walk_f32): device-side
+    tip motion, fused concentration step, the two recorded strip fluxes and the tip advance, per step, with no
+    interpreter in the loop (demo_2d_LBM_JRL_C_cylinder.py:281-362).  `fs`: a FusedStep built with
+    is_convection=True; flags and C are updated in place / ping-ponged.  Returns
+    (h, C, records [nsteps,4] = inflow flux, inflow sum, current flux, current sum, walks, phi_obs, C_vel)."""
+    if not fs.is_convection:
+        raise RuntimeError("conc_walk needs a FusedStep with is_convection=True")
+    B, H, W = _dims(h)
+    nsteps = int(nsteps)
+    h_alt, C_alt = torch.empty_like(h), torch.empty_like(C)
+    phi = torch.empty_like(C)
+    C_vel = torch.empty((1, 2, H, W), dtype=h.dtype, device=h.device)
+    if records is None:
+        records = torch.zeros((max(nsteps, 1), 4), dtype=torch.float32, device=h.device)
+    d, _, _, _, keep = fs._desc(h, flags, C, C_vel, h_alt, C_alt, None, True, phi, None, mesh_grid, None, 0, False, None, None,
+                                clamp01, None, None, 0, None)
+    w = N.WalkDesc()
+    w.step = d
+    t = w.tip
+    t.H, t.W, t.is_negative = H, W, int(bool(is_negative))
+    t.Rg_radius, t.radius_obs_int = int(Rg_radius), int(radius_obs_int)
+    t.box_cx, t.box_radius, t.vel_obs_conv = float(box_center_x), float(box_radius), float(vel_obs_conv)
+    t.mesh_grid = d.mesh_grid
+    w.walks, w.vel_obs_conv, w.dx, w.dt = float(walks), float(vel_obs_conv), float(dx), float(dt)
+    w.box_radius, w.inflow_height, w.x_interval = float(box_radius), float(inflow_height), float(x_interval)
+    snaps = vel_snaps.contiguous()
+    w.vel_snaps = N.tensor_ptr(snaps, "vel_snaps", shape=(snaps.shape[0], 2, H, W), like=h)
+    w.n_snaps = int(snaps.shape[0])
+    w.records = N.tensor_ptr(records, "records", shape=(max(nsteps, 1), 4), like=h)
+    N.call("jrl_conc_walk_f32", ctypes.byref(w), nsteps, like=h)
+    N.launch_count += max(0, 4 * nsteps - 1)
+    try:
+        torch.autograd.graph.increment_version(flags)
+    except AttributeError:
+        flags.add_(0)
+    odd = nsteps % 2 == 1
+    return (h_alt if odd else h), (C_alt if odd else C), records, float(w.walks), phi, C_vel
 
 
 def new_sums(device):

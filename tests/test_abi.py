@@ -55,6 +55,8 @@ def test_descriptor_structs_match_the_header():
     import jrl_native
     assert [n for n, _ in jrl_native.StepDesc._fields_] == header_struct_fields("jrl_step_desc")
     assert [n for n, _ in jrl_native.CollideDesc._fields_] == header_struct_fields("jrl_collide_desc")
+    assert [n for n, _ in jrl_native.TipDesc._fields_] == header_struct_fields("jrl_tip_desc")
+    assert [n for n, _ in jrl_native.WalkDesc._fields_] == header_struct_fields("jrl_walk_desc")
 
 
 def test_library_exports_every_declared_symbol():

@@ -10,7 +10,7 @@ import pytest
 import torch
 
 import jrl_scenarios as S
-from fused_cases import (FUSED_CASES, RUN_CASES, assert_identical, check_run_equals_steps, check_run_sums_series,
+from fused_cases import (FUSED_CASES, RUN_CASES, assert_identical, check_run_equals_steps, check_device_tip, check_run_sums_series,
                          check_sums, check_tile_mask, run_pair)
 from golden_cases import CASES
 from util import compare_outputs, load_golden, rel_l2
@@ -83,7 +83,7 @@ def test_vector_widths_agree(cuda_api, dev):
 
 
 @pytest.mark.parametrize("op,conv,axisym", [("bgk", False, 0), ("mrt", False, 0), ("kbc", False, 0), ("bgk", True, 1),
-                                            ("bgk", True, 0)])
+                                            ("bgk", True, 0), ("bgk", True, 2)])
 @pytest.mark.parametrize("W", [1024, 2064])
 def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym, W):
     """force_vec = 8 (TMA-pipelined kernel: 1024-cell tiles, partial last tile at W = 2064, halo wrap at
@@ -95,6 +95,7 @@ def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym
     st = S.random_state((H, W), 9, dev, obstacles=True, io_cells=True)
     flags = st["flags"].clone()
     flags[:, :, 8:30, 100:W - 100] = 1          # a large all-FLUID region so that the staged (bulk) path runs too
+    flags[:, :, 12:26, 0:24] = 1                # ... including groups on the x symmetry axis (column 0)
     fs = jrl_step.FusedStep(P, operator=op, kbc_type=133 if op == "kbc" else None, is_convection=conv,
                             tau_D=0.8 if conv else None)
     mesh = cuda_api.create_2d_meshgrid_tensor((1, 1, H, W), device=dev) + 0.5
@@ -115,6 +116,11 @@ def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym
 @pytest.mark.parametrize("name", list(RUN_CASES))
 def test_run_equals_steps(cuda_api, dev, name):
     check_run_equals_steps(cuda_api, dev, name)
+
+
+@pytest.mark.parametrize("is_negative,fused", [(True, True), (False, True), (True, False)])
+def test_device_tip_motion(cuda_api, dev, is_negative, fused):
+    check_device_tip(cuda_api, dev, is_negative=is_negative, fused=fused)
 
 
 def test_run_sums_series(cuda_api, dev):

@@ -78,6 +78,20 @@ def native_cases(S, api, dev):
             emit(config=name, variant=label[fused], grid=list(kw["res"]), us_per_step=round(us, 2), mlups=round(cells / us, 1))
 
 
+def walk_cases(S, api, dev):
+    """C4 native (128 x 64) walk loop with velocity snapshots interpolated as the demo does: host torch ops per step,
+    device-side tip motion (1 launch), and the whole loop in one library call (jrl_conc_walk_f32)."""
+    res = (128, 64)
+    mesh = api.create_2d_meshgrid_tensor(size=(1, 1, *res), device=dev, dtype=torch.float32) + 0.5
+    snaps = torch.cat([S.analytic_tip_velocity(mesh, 20.50000000000001 + k * 0.1, 6.50000000000001) for k in range(700)], dim=0).contiguous()
+    kw = dict(res=res, balance_steps=0, vel_snaps=snaps, x_interval=0.1, fused=True)
+    for label, extra, (n1, n2) in (("fused step + host torch ops for the tip (demo loop)", {}, (100, 600)),
+                                   ("fused step + device-side tip motion (jrl_tip_prepare_conc_f32), Python loop", dict(device_tip=True), (100, 600)),
+                                   ("jrl_conc_walk_f32: tip motion + step + flux records, whole loop in one library call", dict(device_tip="run"), (1000, 6000))):
+        us = scenario_us_per_step(S, api, dev, "jrl_conc", dict(kw, **extra), "walk_steps", n1, n2)
+        emit(config="c4_conc_walk", variant=label, grid=list(res), us_per_step=round(us, 2), mlups=round(res[0] * res[1] / us, 1))
+
+
 def big_cases(S, api, dev, G):
     import jrl_step
     import bench
@@ -197,6 +211,8 @@ def main():
     only = set(args.only.split(","))
     if "native" in only and world == 1:
         native_cases(S, api, dev)
+    if ("native" in only or "walk" in only) and world == 1:
+        walk_cases(S, api, dev)
     if "big" in only and world == 1:
         big_cases(S, api, dev, args.big)
     if "c4big" in only:
