@@ -39,6 +39,9 @@ def main():
     ap.add_argument("--balance", type=int, default=200)
     ap.add_argument("--walk", type=int, default=1000)
     ap.add_argument("--members", type=int, default=0, help="members in total (default: one per rank)")
+    ap.add_argument("--mode", default="fast", choices=["demo", "fast"],
+                    help="demo: stage B as the demo drives it (host torch ops for the tip every step); fast: stage B's "
+                         "walk loop in one library call (jrl_conc_walk_f32)")
     args = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
@@ -59,7 +62,8 @@ def main():
         a = S.jrl_fluid(api, dev, res=(128, 64), steps=args.steps_a, gravity_strength=g, vel_obs=vel_obs)
         u = torch.from_numpy(a["vel"]).to(dev) / vel_obs
         b = S.jrl_conc(api, dev, res=(128, 64), balance_steps=args.balance, walk_steps=args.walk, is_negative=neg,
-                       clamp=neg, vel_field=lambda mesh, walks: u.clone(), fused=True)
+                       clamp=neg, vel_snaps=u.reshape(1, 2, 128, 64).contiguous(), fused=True,
+                       device_tip="run" if args.mode == "fast" else False)
         return float(b["current"][-1]), float(b["C"].sum())
 
     torch.cuda.synchronize()
@@ -79,7 +83,7 @@ def main():
         print(json.dumps({"config": "batch_validation ensemble (cylinder geometry, native 128x64)", "n_gpus": world, "members": total,
                           "steps_per_member": {"stage_a": args.steps_a, "balance": args.balance, "walk": args.walk},
                           "wall_s": round(wall, 3), "per_rank_s": [round(float(x.item()), 3) for x in ts],
-                          "member_steps_per_s": round(steps / wall, 1), "communication": "none (replicas)",
+                          "member_steps_per_s": round(steps / wall, 1), "communication": "none (replicas)", "mode": args.mode,
                           "rank0_last_current": results[0][0] if results else None}), flush=True)
     if world > 1:
         dist.barrier()
