@@ -261,6 +261,41 @@ typedef struct jrl_walk_desc
 } jrl_walk_desc;
 int jrl_conc_walk_f32(jrl_walk_desc *w, int nsteps, void *stream);
 
+/* Stage A (axisymmetric tip flow, demo_2d_LBM_JRL_fluid_cylinder.py).  jrl_tip_prepare_fluid_f32: the per-step host
+ * work of :205-214 in one launch -- phi_obs (CalculateObsPhi :39-49, united with the top wall), the wall velocity field
+ * obs_vel = (0, vel_obs) inside the tip and 0 outside, flags = OBSTACLE and vel = (0, vel_obs) inside the tip
+ * (rows < walks_int, columns < Rg_radius).  flags / vel in place; phi_obs [1,1,H,W], obs_vel [1,2,H,W] fully written. */
+typedef struct jrl_tip_fluid_desc
+{
+    int H, W;
+    int walks_int, Rg_radius;
+    float box_cx, box_cy, box_radius, vel_obs;
+    const float *mesh_grid;
+    uint8_t *flags;
+    float *vel;
+    float *phi_obs;
+    float *obs_vel;
+} jrl_tip_fluid_desc;
+int jrl_tip_prepare_fluid_f32(const jrl_tip_fluid_desc *d, void *stream);
+
+/* Stage-A walk loop below the ABI (:203-264): per step jrl_tip_prepare_fluid_f32 -> jrl_stream_f32 (phi_obs, rho, vel)
+ * -> jrl_wall_f32 -> jrl_moments_f32 -> jrl_collide_f32 (BGK + axisymmetric source) -> walks += vel_obs * dt.
+ * f[3]: population buffers, f[0] holds the state before and after the call; rho[2] / vel[2]: moment pairs, pair 0
+ * current on entry, pair `current` on return.  `collide`: op, axisym, dx, dt, tau, flags, force, mesh_grid (f, rho, vel,
+ * f_out are filled per step); `tip`: the static fields (H, W, Rg_radius, box_cx, box_radius, vel_obs, mesh_grid, phi_obs,
+ * obs_vel buffers). */
+typedef struct jrl_fluid_walk_desc
+{
+    jrl_collide_desc collide;
+    jrl_tip_fluid_desc tip;
+    double walks, vel_obs, box_radius;
+    float *f[3];
+    float *rho[2];
+    float *vel[2];
+    int current;
+} jrl_fluid_walk_desc;
+int jrl_fluid_walk_f32(jrl_fluid_walk_desc *w, int nsteps, void *stream);
+
 /* ---- row-slab halo helpers (multi-GPU) ----------------------------------------------------------
  * Pack / unpack `nrows` full rows of all C planes of a [C,Hloc,W] slab starting at row `row`
  * into a contiguous [C,nrows,W] staging buffer (the message NCCL sends to the neighbour rank). */

@@ -482,6 +482,33 @@ __global__ void __launch_bounds__(kThreads) k_tip_conc(jrl_tip_desc d)
     d.C_vel[HW + i] = vy;
 }
 
+// Stage A (axisymmetric tip flow): per-step host work of demo_2d_LBM_JRL_fluid_cylinder.py:205-214 in one
+// launch -- CalculateObsPhi (:39-49), the wall velocity field, and the OBSTACLE / velocity stamps inside the tip.
+__global__ void __launch_bounds__(kThreads) k_tip_fluid(jrl_tip_fluid_desc d)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long HW = (long long)d.H * d.W;
+    if (i >= HW)
+        return;
+    const int y = (int)(i / d.W), x = (int)(i - (long long)y * d.W);
+    const float mx = d.mesh_grid[i], my = d.mesh_grid[HW + i];
+    const float tx = (mx - d.box_cx) - d.box_radius;
+    const float ty = (my - d.box_cy) - d.box_radius;
+    float phi = tx > ty ? tx : ty;
+    const float top = -(my - (float)d.H);
+    phi = phi < top ? phi : top;
+    d.phi_obs[i] = phi;
+    const bool inside = y < d.walks_int && x < d.Rg_radius;
+    d.obs_vel[i] = 0.f;
+    d.obs_vel[HW + i] = inside ? d.vel_obs : 0.f;
+    if (inside)
+    {
+        d.flags[i] = CT_OBSTACLE;
+        d.vel[i] = 0.f;
+        d.vel[HW + i] = d.vel_obs;
+    }
+}
+
 // ---- halo staging ----------------------------------------------------------------------------------
 __global__ void k_halo_copy(float *__restrict__ dst, const float *__restrict__ src, int C, long long plane_dst,
                             long long plane_src, long long off_dst, long long off_src, long long n)
@@ -771,6 +798,68 @@ int jrl_tip_prepare_conc_f32(const jrl_tip_desc *d, void *stream)
     JRL_REQUIRE(d->C_vel != d->vel0 && d->C_vel != d->vel1, fn, "C_vel must not alias the velocity snapshots");
     JRL_LAUNCH(k_tip_conc, blocks_for((long long)d->H * d->W), kThreads, (cudaStream_t)stream, *d);
     return check_launch(fn);
+}
+
+int jrl_tip_prepare_fluid_f32(const jrl_tip_fluid_desc *d, void *stream)
+{
+    const char *fn = "jrl_tip_prepare_fluid_f32";
+    JRL_REQUIRE(d, fn, "null descriptor");
+    JRL_REQUIRE(d->H >= 3 && d->W >= 3, fn, "H, W >= 3 required");
+    JRL_REQUIRE(d->mesh_grid && d->flags && d->vel && d->phi_obs && d->obs_vel, fn, "mesh_grid, flags, vel, phi_obs, obs_vel required");
+    JRL_LAUNCH(k_tip_fluid, blocks_for((long long)d->H * d->W), kThreads, (cudaStream_t)stream, *d);
+    return check_launch(fn);
+}
+
+// Stage-A walk loop below the ABI (demo_2d_LBM_JRL_fluid_cylinder.py:203-264): per step tip motion -> streaming
+// with interpolated bounce-back -> moving-wall reconstruction -> moments -> BGK collision with the axisymmetric
+// source (the one operator chain that cannot be a single pass, see jrl_step_f32) -> walks += vel_obs dt.
+int jrl_fluid_walk_f32(jrl_fluid_walk_desc *w, int nsteps, void *stream)
+{
+    const char *fn = "jrl_fluid_walk_f32";
+    JRL_REQUIRE(w, fn, "null descriptor");
+    JRL_REQUIRE(nsteps >= 0, fn, "nsteps must be >= 0");
+    JRL_REQUIRE(w->f[0] && w->f[1] && w->f[2] && w->rho[0] && w->rho[1] && w->vel[0] && w->vel[1], fn,
+                "three population buffers and two (rho, vel) pairs required");
+    jrl_tip_fluid_desc t = w->tip;
+    jrl_collide_desc c = w->collide;
+    JRL_REQUIRE(c.B == 1 && c.H == t.H && c.W == t.W && c.mesh_grid && c.flags, fn, "collide descriptor: B = 1, same extents, mesh_grid and flags required");
+    double walks = w->walks;
+    int cur = 0;  // index of the current (rho, vel) pair
+    float *fa = w->f[0], *fb = w->f[1], *fc = w->f[2];
+    for (int i = 0; i < nsteps; ++i)
+    {
+        const int walks_int = (int)(walks + 0.5 * c.dx);
+        JRL_REQUIRE(walks_int >= 1 && walks_int < t.H, fn, "the tip left the grid");
+        t.walks_int = walks_int;
+        t.box_cy = (float)(walks - w->box_radius);
+        t.flags = const_cast<uint8_t *>(c.flags);
+        t.vel = w->vel[cur];
+        int rc = jrl_tip_prepare_fluid_f32(&t, stream);
+        if (rc != 0)
+            return rc;
+        rc = jrl_stream_f32(c.flags, fa, t.phi_obs, fb, w->rho[cur], w->vel[cur], nullptr, -1.0, c.axisym, 1, c.H, c.W, stream);
+        if (rc != 0)
+            return rc;
+        rc = jrl_wall_f32(c.dt, c.dx, c.tau, w->vel[cur], c.flags, fb, fc, t.phi_obs, t.obs_vel, c.axisym, 1, c.H, c.W, stream);
+        if (rc != 0)
+            return rc;
+        rc = jrl_moments_f32(fc, w->rho[cur], w->vel[cur], c.flags, w->rho[1 - cur], w->vel[1 - cur], 0, 0.f, c.dx / c.dt, 1, c.H, c.W, stream);
+        if (rc != 0)
+            return rc;
+        cur = 1 - cur;
+        c.f = fc;
+        c.rho = w->rho[cur];
+        c.vel = w->vel[cur];
+        c.f_out = fa;
+        rc = jrl_collide_f32(&c, stream);
+        if (rc != 0)
+            return rc;
+        walks += w->vel_obs * c.dt;
+    }
+    (void)fb;
+    w->walks = walks;
+    w->current = cur;
+    return JRL_OK;
 }
 
 int jrl_halo_pack_f32(const float *field, float *staging, int C, int Hloc, int W, int row, int nrows, void *stream)

@@ -54,6 +54,17 @@ class TipDesc(Structure):  # struct jrl_tip_desc
                 ("C", c_void_p), ("vel0", c_void_p), ("vel1", c_void_p), ("phi_obs", c_void_p), ("C_vel", c_void_p)]
 
 
+class TipFluidDesc(Structure):  # struct jrl_tip_fluid_desc
+    _fields_ = [("H", c_int), ("W", c_int), ("walks_int", c_int), ("Rg_radius", c_int), ("box_cx", c_float), ("box_cy", c_float),
+                ("box_radius", c_float), ("vel_obs", c_float), ("mesh_grid", c_void_p), ("flags", c_void_p), ("vel", c_void_p),
+                ("phi_obs", c_void_p), ("obs_vel", c_void_p)]
+
+
+class FluidWalkDesc(Structure):  # struct jrl_fluid_walk_desc
+    _fields_ = [("collide", CollideDesc), ("tip", TipFluidDesc), ("walks", c_double), ("vel_obs", c_double),
+                ("box_radius", c_double), ("f", c_void_p * 3), ("rho", c_void_p * 2), ("vel", c_void_p * 2), ("current", c_int)]
+
+
 class WalkDesc(Structure):  # struct jrl_walk_desc
     _fields_ = [("step", StepDesc), ("tip", TipDesc), ("walks", c_double), ("vel_obs_conv", c_double), ("dx", c_double),
                 ("dt", c_double), ("box_radius", c_double), ("inflow_height", c_double), ("x_interval", c_double),
@@ -83,6 +94,8 @@ PROTOTYPES = {
     "jrl_tile_mask_bytes": [_i, _i, _i],
     "jrl_tile_mask_u8": [_vp, _vp, _i, _i, _i, _vp],
     "jrl_tip_prepare_conc_f32": [POINTER(TipDesc), _vp],
+    "jrl_tip_prepare_fluid_f32": [POINTER(TipFluidDesc), _vp],
+    "jrl_fluid_walk_f32": [POINTER(FluidWalkDesc), _i, _vp],
     "jrl_conc_walk_f32": [POINTER(WalkDesc), _i, _vp],
     "jrl_halo_pack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "jrl_halo_unpack_f32": [_vp, _vp, _i, _i, _i, _i, _i, _vp],

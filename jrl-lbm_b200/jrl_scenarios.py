@@ -211,7 +211,7 @@ def tip_phi(api, mesh_grid, box_center, box_radius, is_negative=True):
 
 def jrl_fluid(api, device, res=(128, 64), steps=200, Re=3e-4, gravity_strength=0.0, radius_obs=6.50000000000001,
               inflow_height=20.50000000000001, Rg=4, vel_obs=None, x_interval=0.1, dx=1, dt=1, tau=1.0,
-              snapshots=()):
+              snapshots=(), device_tip=False):
     """Stage A with the demo's per-step host work (phi / flags / wall velocity restamp) kept as
     torch ops.  `vel_obs` defaults to Re*visc/radius_obs as in the demo (:78); tests pass a
     larger value so the tip crosses cells within a few hundred steps.  `gravity_strength` is
@@ -256,6 +256,18 @@ def jrl_fluid(api, device, res=(128, 64), steps=200, Re=3e-4, gravity_strength=0
     vel[..., 0, 0:walks_int, 0:Rg_radius] = 0
     vel[..., 1, 0:walks_int, 0:Rg_radius] = vel_obs
     out = {}
+    if device_tip == "run":  # extension of this repo: the whole loop below the C ABI (jrl_fluid_walk_f32)
+        import jrl_step
+        done = 0
+        for stop in sorted(set(int(x) for x in snapshots if 0 < int(x) < steps)) + [steps]:
+            f, density, vel, walks, phi_obs, phi_obs_vel = jrl_step.fluid_walk(
+                collision_f, f, flags, density, vel, mesh_grid, force, walks, stop - done, box_center_x=float(box_center[0]),
+                box_radius=box_radius, Rg_radius=Rg_radius, vel_obs=vel_obs, tau=tau, dx=dx, dt=dt)
+            done = stop
+            if done in snapshots:
+                out[f"snap_{done}_rho"] = _np(density)
+                out[f"snap_{done}_vel"] = _np(vel)
+        steps = 0
     for step in range(steps):
         walks_int = int(walks + 0.5 * dx)
         box_center[1] = walks - box_radius

@@ -224,6 +224,52 @@ def conc_walk(fs, h, flags, C, mesh_grid, vel_snaps, walks, nsteps, *, box_cente
     return (h_alt if odd else h), (C_alt if odd else C), records, float(w.walks), phi, C_vel
 
 
+def fluid_walk(collision, f, flags, rho, vel, mesh_grid, force, walks, nsteps, *, box_center_x, box_radius, Rg_radius, vel_obs,
+               tau, dx=1.0, dt=1.0):
+    """`nsteps` of the JRL fluid demos' loop (stage A, demo_2d_LBM_JRL_fluid_cylinder.py:203-264) in ONE library call
+    (jrl_fluid_walk_f32): device-side tip motion, streaming with interpolated bounce-back, moving-wall reconstruction,
+    moments, BGK collision with the axisymmetric source, tip advance.  `collision`: the LBMCollision2d object (axisymmetric
+    type and operator are read from it).  flags and the moment tensors are updated in place / ping-ponged.
+    Returns (f, rho, vel, walks, phi_obs, obs_vel)."""
+    B, H, W = _dims(f)
+    if B != 1:
+        raise RuntimeError("fluid_walk: batch size 1 only")
+    w = N.FluidWalkDesc()
+    c = w.collide
+    c.B, c.H, c.W = 1, H, W
+    c.axisym = int(collision.axisymmetric_type)
+    c.op, c.kbc_type, c.is_convection = N.OP_BGK, 0, 0
+    c.dx, c.dt, c.tau = float(dx), float(dt), float(tau)
+    c.flags = N.tensor_ptr(flags, "flags", torch.uint8, (1, 1, H, W), like=f)
+    force = _full(force, (1, 2, H, W), "force", f)
+    c.force = N.tensor_ptr(force, "force", shape=(1, 2, H, W), like=f, optional=True)
+    c.mesh_grid = N.tensor_ptr(mesh_grid, "mesh_grid", shape=(1, 2, H, W), like=f)
+    phi, obs_vel = torch.empty_like(rho), torch.empty_like(vel)
+    t = w.tip
+    t.H, t.W, t.Rg_radius = H, W, int(Rg_radius)
+    t.box_cx, t.box_radius, t.vel_obs = float(box_center_x), float(box_radius), float(vel_obs)
+    t.mesh_grid = c.mesh_grid
+    t.phi_obs = N.tensor_ptr(phi, "phi_obs", shape=(1, 1, H, W), like=f)
+    t.obs_vel = N.tensor_ptr(obs_vel, "obs_vel", shape=(1, 2, H, W), like=f)
+    w.walks, w.vel_obs, w.box_radius = float(walks), float(vel_obs), float(box_radius)
+    fb, fc = torch.empty_like(f), torch.empty_like(f)
+    rho2, vel2 = torch.empty_like(rho), torch.empty_like(vel)
+    w.f[0] = N.tensor_ptr(f, "f", shape=(1, 9, H, W)).value
+    w.f[1], w.f[2] = fb.data_ptr(), fc.data_ptr()
+    w.rho[0] = N.tensor_ptr(rho, "rho", shape=(1, 1, H, W), like=f).value
+    w.rho[1] = rho2.data_ptr()
+    w.vel[0] = N.tensor_ptr(vel, "vel", shape=(1, 2, H, W), like=f).value
+    w.vel[1] = vel2.data_ptr()
+    N.call("jrl_fluid_walk_f32", ctypes.byref(w), int(nsteps), like=f)
+    N.launch_count += max(0, 5 * int(nsteps) - 1)
+    try:
+        torch.autograd.graph.increment_version(flags)
+    except AttributeError:
+        flags.add_(0)
+    cur = int(w.current)
+    return f, (rho2 if cur else rho), (vel2 if cur else vel), float(w.walks), phi, obs_vel
+
+
 def new_sums(device):
     """Zeroed accumulator for FusedStep.step(sums=...)."""
     return torch.zeros((N.SUM_SLOTS, 4), dtype=torch.float64, device=device)

@@ -167,3 +167,14 @@ def check_device_tip(api, device, is_negative=True, fused=True):
         for k in ("inflow", "current"):
             a, b = np.asarray(run[k], np.float64), np.asarray(host[k], np.float64)
             assert np.linalg.norm(a - b) <= 1e-5 * np.linalg.norm(b), k
+
+
+def check_fluid_walk(api, device, gravity=2e-5):
+    """Stage-A loop in one library call (jrl_fluid_walk_f32) equals the demo's loop (solver objects + host torch ops
+    for the tip) bit for bit."""
+    kw = dict(res=(48, 32), steps=70, radius_obs=2.50000000000001, inflow_height=8.50000000000001, Rg=3, vel_obs=0.02,
+              gravity_strength=gravity, snapshots=(25,))
+    host = S.jrl_fluid(api, device, **kw)
+    run = S.jrl_fluid(api, device, device_tip="run", **kw)
+    assert_identical(host, run)
+    assert abs(host["walks"] - run["walks"]) < 1e-12

@@ -38,7 +38,7 @@ def header_struct_fields(name):
         if not decl:
             continue
         for part in decl.split(","):
-            fields.append(re.findall(r"\w+", part)[-1])
+            fields.append(re.findall(r"\w+", re.sub(r"\[.*?\]", "", part))[-1])
     return fields
 
 
@@ -57,6 +57,8 @@ def test_descriptor_structs_match_the_header():
     assert [n for n, _ in jrl_native.CollideDesc._fields_] == header_struct_fields("jrl_collide_desc")
     assert [n for n, _ in jrl_native.TipDesc._fields_] == header_struct_fields("jrl_tip_desc")
     assert [n for n, _ in jrl_native.WalkDesc._fields_] == header_struct_fields("jrl_walk_desc")
+    assert [n for n, _ in jrl_native.TipFluidDesc._fields_] == header_struct_fields("jrl_tip_fluid_desc")
+    assert [n for n, _ in jrl_native.FluidWalkDesc._fields_] == header_struct_fields("jrl_fluid_walk_desc")
 
 
 def test_library_exports_every_declared_symbol():

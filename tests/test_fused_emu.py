@@ -2,7 +2,7 @@
 import pytest
 import torch
 
-from fused_cases import (FUSED_CASES, RUN_CASES, assert_identical, check_run_equals_steps, check_device_tip, check_run_sums_series,
+from fused_cases import (FUSED_CASES, RUN_CASES, assert_identical, check_run_equals_steps, check_device_tip, check_fluid_walk, check_run_sums_series,
                          check_sums, check_tile_mask, run_pair)
 
 
@@ -32,3 +32,8 @@ def test_run_sums_series(emu_api):
 @pytest.mark.parametrize("is_negative,fused", [(True, True), (False, True), (True, False)])
 def test_device_tip_motion(emu_api, is_negative, fused):
     check_device_tip(emu_api, torch.device("cpu"), is_negative=is_negative, fused=fused)
+
+
+@pytest.mark.parametrize("gravity", [2e-5, 0.0])
+def test_fluid_walk(emu_api, gravity):
+    check_fluid_walk(emu_api, torch.device("cpu"), gravity)

@@ -10,7 +10,7 @@ import pytest
 import torch
 
 import jrl_scenarios as S
-from fused_cases import (FUSED_CASES, RUN_CASES, assert_identical, check_run_equals_steps, check_device_tip, check_run_sums_series,
+from fused_cases import (FUSED_CASES, RUN_CASES, assert_identical, check_run_equals_steps, check_device_tip, check_fluid_walk, check_run_sums_series,
                          check_sums, check_tile_mask, run_pair)
 from golden_cases import CASES
 from util import compare_outputs, load_golden, rel_l2
@@ -121,6 +121,11 @@ def test_run_equals_steps(cuda_api, dev, name):
 @pytest.mark.parametrize("is_negative,fused", [(True, True), (False, True), (True, False)])
 def test_device_tip_motion(cuda_api, dev, is_negative, fused):
     check_device_tip(cuda_api, dev, is_negative=is_negative, fused=fused)
+
+
+@pytest.mark.parametrize("gravity", [2e-5, 0.0])
+def test_fluid_walk(cuda_api, dev, gravity):
+    check_fluid_walk(cuda_api, dev, gravity)
 
 
 def test_run_sums_series(cuda_api, dev):

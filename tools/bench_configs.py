@@ -85,6 +85,9 @@ def walk_cases(S, api, dev):
     mesh = api.create_2d_meshgrid_tensor(size=(1, 1, *res), device=dev, dtype=torch.float32) + 0.5
     snaps = torch.cat([S.analytic_tip_velocity(mesh, 20.50000000000001 + k * 0.1, 6.50000000000001) for k in range(700)], dim=0).contiguous()
     kw = dict(res=res, balance_steps=0, vel_snaps=snaps, x_interval=0.1, fused=True)
+    us = scenario_us_per_step(S, api, dev, "jrl_fluid", dict(res=res, gravity_strength=2e-5, device_tip="run"), "steps", 1000, 6000)
+    emit(config="c5_fluid_stageA", variant="jrl_fluid_walk_f32: tip motion + stream + wall + moments + collide, whole loop in one library call",
+         grid=list(res), us_per_step=round(us, 2), mlups=round(res[0] * res[1] / us, 1))
     for label, extra, (n1, n2) in (("fused step + host torch ops for the tip (demo loop)", {}, (100, 600)),
                                    ("fused step + device-side tip motion (jrl_tip_prepare_conc_f32), Python loop", dict(device_tip=True), (100, 600)),
                                    ("jrl_conc_walk_f32: tip motion + step + flux records, whole loop in one library call", dict(device_tip="run"), (1000, 6000))):

@@ -40,8 +40,8 @@ def main():
     ap.add_argument("--walk", type=int, default=1000)
     ap.add_argument("--members", type=int, default=0, help="members in total (default: one per rank)")
     ap.add_argument("--mode", default="fast", choices=["demo", "fast"],
-                    help="demo: stage B as the demo drives it (host torch ops for the tip every step); fast: stage B's "
-                         "walk loop in one library call (jrl_conc_walk_f32)")
+                    help="demo: stage B as the demo drives it (host torch ops for the tip every step); fast: both stages' "
+                         "loops in one library call each (jrl_fluid_walk_f32, jrl_conc_walk_f32)")
     args = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
@@ -59,7 +59,8 @@ def main():
 
     def member(m):
         g, neg = MEMBERS[m % len(MEMBERS)]
-        a = S.jrl_fluid(api, dev, res=(128, 64), steps=args.steps_a, gravity_strength=g, vel_obs=vel_obs)
+        a = S.jrl_fluid(api, dev, res=(128, 64), steps=args.steps_a, gravity_strength=g, vel_obs=vel_obs,
+                        device_tip="run" if args.mode == "fast" else False)
         u = torch.from_numpy(a["vel"]).to(dev) / vel_obs
         b = S.jrl_conc(api, dev, res=(128, 64), balance_steps=args.balance, walk_steps=args.walk, is_negative=neg,
                        clamp=neg, vel_snaps=u.reshape(1, 2, 128, 64).contiguous(), fused=True,
