@@ -23,6 +23,9 @@
 #ifndef JRL_PIPE_CW
 #define JRL_PIPE_CW 512
 #endif
+#ifndef JRL_EXP_FAST_OP
+#define JRL_EXP_FAST_OP OP_BGK
+#endif
 #ifndef JRL_PIPE_STAGES
 #define JRL_PIPE_STAGES 2
 #endif
@@ -909,8 +912,8 @@ static int launch(const StepArgs &a, int B, cudaStream_t s)
 {
     const unsigned tpr = (unsigned)((a.g.W + CW - 1) / CW), rows = (unsigned)(a.row_end - a.row_begin);
     const unsigned total = (unsigned)B * rows * tpr;
-#ifdef JRL_EXP_FAST_BUILD  // experiment builds (tools/): BGK only, compiles in a fraction of the time
-    return launch_one<OP_BGK, 0>(a, total, tpr, rows, s);
+#ifdef JRL_EXP_FAST_BUILD  // experiment builds (tools/): one operator only (JRL_EXP_FAST_OP, default BGK), compiles in a fraction of the time
+    return launch_one<JRL_EXP_FAST_OP, 0>(a, total, tpr, rows, s);
 #else
     if (a.cp.convection)
         return a.g.axisym == AXI_X ? launch_one<OP_BGK, 1>(a, total, tpr, rows, s)
@@ -918,8 +921,8 @@ static int launch(const StepArgs &a, int B, cudaStream_t s)
                                                           : launch_one<OP_BGK, 3>(a, total, tpr, rows, s));
     if (a.cp.op == OP_BGK)
         return launch_one<OP_BGK, 0>(a, total, tpr, rows, s);
-    if (a.cp.op == OP_MRT)
-        return launch_one<OP_MRT, 0>(a, total, tpr, rows, s);
+    if (a.cp.op == OP_MRT)  // 2 cells per consumer thread, 3 stages (see the dispatch note in step_once)
+        return launch_cfg<OP_MRT, 0, 2, 3, JRL_PIPE_MINB>(a, total, tpr, rows, s);
     return launch_one<OP_KBC, 0>(a, total, tpr, rows, s);
 #endif
 }
@@ -991,7 +994,7 @@ static int launch_step(const StepArgs &a, int B, cudaStream_t s)
         JRL_LAUNCH(kern, grid, block, s, a);         \
     } while (0)
 #ifdef JRL_EXP_FAST_BUILD
-    JRL_STEP(OP_BGK, 0);
+    JRL_STEP(JRL_EXP_FAST_OP, 0);
     return 0;
 #endif
     if (a.cp.convection)
@@ -1123,12 +1126,14 @@ static int step_once(const jrl_step_desc *d, void *stream)
         }
     }
 #ifndef JRL_HOST_EMU
-    // automatic choice: the pipelined kernel wins for BGK (memory-bound); MRT / KBC are bound by their
-    // arithmetic and run faster in the register kernel (3.8 vs 3.1 TB/s MRT at 8192^2)
+    // automatic choice: the pipelined kernel wins for BGK (memory-bound, 4 cells per consumer thread) and for MRT
+    // with 2 cells per consumer thread (16 consumer warps per SM for the 81-FMA matvec: 4.7 TB/s at 8192^2 against
+    // 4.1 in the register kernel and 3.95 with 4 cells per thread); KBC is bound by its instruction count (~940 per
+    // cell, 19 IEEE divisions) and runs faster in the register kernel (1.6 vs 0.9-1.4 TB/s)
     // (the concentration form on real geometries -- tip block, inlet column, symmetry axis -- has too many groups
     // on the generic path for the pipelined kernel's eight consumer warps per SM: 3.4 ms vs 1.9 ms per step on
     // the scaled C4 grid, so it also defaults to the register kernel; force_vec = 8 selects the pipeline)
-    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4 && d->op == JRL_OP_BGK && !d->is_convection))
+    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4 && (d->op == JRL_OP_BGK || d->op == JRL_OP_MRT) && !d->is_convection))
     {
         const bool ok = vec == 4 && pipe::eligible(a, d->B);
         JRL_REQUIRE(ok || d->force_vec == 0, fn, "pipelined kernel needs W % 16 == 0, W >= 512 and 16-byte aligned planes");

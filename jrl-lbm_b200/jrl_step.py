@@ -147,7 +147,7 @@ class FusedStep:
         d.wall_phi = N.tensor_ptr(wall_phi, "wall_phi", shape=(B, 1, Hs, W), like=f, optional=True)
         mask = None
         if (self.use_tile_mask and W % 16 == 0 and W >= 512 and flags.data_ptr() % 16 == 0
-                and (force_vec == 8 or (force_vec == 0 and self.op == N.OP_BGK and not self.is_convection))):
+                and (force_vec == 8 or (force_vec == 0 and self.op in (N.OP_BGK, N.OP_MRT) and not self.is_convection))):
             mask = self._tile_mask(flags, B, Hs, W)
         d.tile_mask = None if mask is None else mask.data_ptr()
         return d, f_out, rho_out, vel_out, (force, mask)
