@@ -39,6 +39,9 @@ def main():
     ap.add_argument("--balance", type=int, default=200)
     ap.add_argument("--walk", type=int, default=1000)
     ap.add_argument("--members", type=int, default=0, help="members in total (default: one per rank)")
+    ap.add_argument("--out", default="", help="directory: per member, hand stage A's velocity to stage B through the field cache "
+                                              "(vel.h5 / vel.h5.npz, as the demos do), keep the final C / h cache and a Tecplot .dat "
+                                              "of the final state streamed off the device by jrl_io.AsyncSnapshotter")
     ap.add_argument("--mode", default="fast", choices=["demo", "fast"],
                     help="demo: stage B as the demo drives it (host torch ops for the tip every step); fast: both stages' "
                          "loops in one library call each (jrl_fluid_walk_f32, jrl_conc_walk_f32)")
@@ -52,7 +55,10 @@ def main():
     import jrl_native
     jrl_native.load()
     import jrl_scenarios as S
+    import jrl_io
     api = S.api_from_src()
+    from src.LBM.utils import io as lbm_io
+    snap = jrl_io.AsyncSnapshotter(depth=2) if args.out else None
     total = args.members or world
     mine = [m for m in range(total) if m % world == rank]
     vel_obs = 0.02  # fast tip so that it crosses cells inside the step budget (tests use the same value)
@@ -62,9 +68,19 @@ def main():
         a = S.jrl_fluid(api, dev, res=(128, 64), steps=args.steps_a, gravity_strength=g, vel_obs=vel_obs,
                         device_tip="run" if args.mode == "fast" else False)
         u = torch.from_numpy(a["vel"]).to(dev) / vel_obs
+        if args.out:  # the stage A -> B coupling file (demo_2d_LBM_JRL_fluid_cylinder.py:266-268, ..._C_cylinder.py:276)
+            d = os.path.join(args.out, "member_%02d" % m)
+            jrl_io.save_fields(os.path.join(d, "vel.h5"), vel=u.reshape(1, 2, 128, 64))
+            u = jrl_io.load_fields(os.path.join(d, "vel.h5"), names=["vel"], device=dev, dtype=torch.float32)["vel"][0]
         b = S.jrl_conc(api, dev, res=(128, 64), balance_steps=args.balance, walk_steps=args.walk, is_negative=neg,
                        clamp=neg, vel_snaps=u.reshape(1, 2, 128, 64).contiguous(), fused=True,
                        device_tip="run" if args.mode == "fast" else False)
+        if args.out:
+            C, h = torch.from_numpy(b["C"]).to(dev), torch.from_numpy(b["h"]).to(dev)
+            jrl_io.save_fields(os.path.join(d, "C_final.h5"), C=C, h=h)
+            zero = torch.zeros_like(C)
+            snap.submit(lambda hst, p=os.path.join(d, "final.dat"): lbm_io.dump_2d_plt_file_C_rho(p, hst["C"], hst["C"], hst["u"], hst["v"], 0, 0),
+                        C=C, u=zero, v=zero)
         return float(b["current"][-1]), float(b["C"].sum())
 
     torch.cuda.synchronize()
@@ -72,6 +88,8 @@ def main():
         dist.barrier()
     t0 = time.perf_counter()
     results = [member(m) for m in mine]
+    if snap is not None:
+        snap.close()
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     t = torch.tensor([dt], dtype=torch.float64, device=dev)
