@@ -62,6 +62,39 @@ constexpr int kThreads = 256;
 #define JRL_LAUNCH(kern, grid, block, stream, ...) kern<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
 #endif
 
+// Programmatic dependent launch for the small, latency-bound grids (the native 130^2 / 128 x 64 runs are chains of
+// dependent 3-6 us kernels): a kernel launched with JRL_LAUNCH_PDL may be scheduled while its predecessor in the stream
+// is still running, and blocks in pdl_enter() -- the FIRST statement of every kernel launched this way -- until the
+// predecessor has completed and its writes are visible (griddepcontrol.wait).  pdl_enter() also releases the kernel's
+// own dependents (griddepcontrol.launch_dependents), so successive launches overlap their launch latency, nothing else.
+// Without the launch attribute both instructions are no-ops.
+#ifdef JRL_HOST_EMU
+#define JRL_LAUNCH_PDL(kern, grid, block, stream, ...) JRL_LAUNCH(kern, grid, block, stream, __VA_ARGS__)
+inline void pdl_enter() {}
+#else
+__device__ __forceinline__ void pdl_enter()
+{
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t stream, Args &&...args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);  // errors are picked up by check_launch() as for <<< >>>
+}
+#define JRL_LAUNCH_PDL(kern, grid, block, stream, ...) jrl::launch_pdl(kern, dim3(grid), dim3(block), stream, __VA_ARGS__)
+#endif
+
 inline unsigned int blocks_for(long long n, int threads = kThreads)
 {
     return (unsigned int)((n + threads - 1) / threads);
@@ -77,6 +110,9 @@ void make_collide(CollideParams &p, SourceParams &sp, int op, int kbc_type, int 
 WallParams make_wall(double dt, double dx, double tau);
 __global__ void k_contact_ring(Grid g, const float *__restrict__ rho_old, const uint8_t *__restrict__ flags,
                                float *__restrict__ rho_new, float tn);
+
+// `nstrips` consecutive strips y0, y0 + 1, ... in ONE launch (one warp each), out2[2 * k] = strip k (defined in ops.cu)
+int strip_flux_n(const float *C, const float *mesh_grid, int y0, int nstrips, int ncol, float *out2, int H, int W, void *stream);
 
 // Number of SMs of the current device (148 on B200); cached.
 int sm_count();

@@ -345,6 +345,7 @@ __global__ void __launch_bounds__(kThreads, VEC == 1 ? JRL_STEP_MIN_BLOCKS_V1 : 
     // Thread -> cells: blockDim = (TX, TY), TX a multiple of 32 so that a warp never straddles rows;
     // x-group = blockIdx.x * TX + threadIdx.x, row = row_begin + blockIdx.y * TY + threadIdx.y,
     // batch element = blockIdx.z.  No integer division.
+    pdl_enter();  // small grids are launched with JRL_LAUNCH_PDL (launch_step); a no-op otherwise
     const Grid &g = a.g;
     const int gpr = g.W / VEC;  // groups per row
     int gx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -987,11 +988,16 @@ static int launch_step(const StepArgs &a, int B, cudaStream_t s)
     const dim3 grid((gpr + tx - 1) / tx, (rows + ty - 1) / ty, (unsigned)B);
     if (grid.y > 65535u || grid.z > 65535u)
         return fail_arg("jrl_step_f32", "more than 65535 row blocks (or batch elements) in one launch: split it with row_begin / row_end");
+    // latency-bound sizes: overlap this launch with the tail of the previous kernel in the stream (common.cuh)
+    const bool pdl = (long long)B * rows * g.W <= (1ll << 19);
 #define JRL_STEP(OPV, CONVV)                         \
     do                                               \
     {                                                \
         auto kern = k_step<VEC, OPV, CONVV>;         \
-        JRL_LAUNCH(kern, grid, block, s, a);         \
+        if (pdl)                                     \
+            JRL_LAUNCH_PDL(kern, grid, block, s, a); \
+        else                                         \
+            JRL_LAUNCH(kern, grid, block, s, a);     \
     } while (0)
 #ifdef JRL_EXP_FAST_BUILD
     JRL_STEP(JRL_EXP_FAST_OP, 0);
@@ -1284,10 +1290,7 @@ extern "C" int jrl_conc_walk_f32(jrl_walk_desc *w, int nsteps, void *stream)
             return rc;
         // -- records on the new C (:344-362): inflow strip at walks_int, current strip at walks_int + 1
         float *rec = w->records + 4ll * i;
-        rc = jrl_strip_flux_f32(d.rho_out, d.mesh_grid, walks_int, t.radius_obs_int, rec, d.H, d.W, stream);
-        if (rc != 0)
-            return rc;
-        rc = jrl_strip_flux_f32(d.rho_out, d.mesh_grid, walks_int + 1, t.radius_obs_int, rec + 2, d.H, d.W, stream);
+        rc = strip_flux_n(d.rho_out, d.mesh_grid, walks_int, 2, t.radius_obs_int, rec, d.H, d.W, stream);  // one launch, two strips
         if (rc != 0)
             return rc;
         const float *fi = d.f_in;

@@ -24,6 +24,7 @@ __global__ void __launch_bounds__(kThreads) k_stream(Grid g, const uint8_t *__re
                                                      const float *__restrict__ f, const float *__restrict__ phi,
                                                      float *__restrict__ f_new, Inflow in)
 {
+    pdl_enter();
     JRL_CELL_PROLOGUE
     float out[9];
     stream_cell<HAS_PHI>(g, f + b * 9 * g.HW, flags + b * g.HW, HAS_PHI ? phi + b * g.HW : nullptr, in,
@@ -55,6 +56,7 @@ __global__ void __launch_bounds__(kThreads) k_moments(Grid g, const float *__res
                                                       const uint8_t *__restrict__ flags, float *__restrict__ rho_new,
                                                       float *__restrict__ vel_new, int use_contact, float c)
 {
+    pdl_enter();
     JRL_CELL_PROLOGUE
     const float *s = f + b * 9 * g.HW + i;
     float fc[9];
@@ -264,6 +266,7 @@ __global__ void __launch_bounds__(kThreads) k_collide(Grid g, const __grid_const
                                                       const float *__restrict__ force, const float *__restrict__ mesh,
                                                       float *__restrict__ f_out)
 {
+    pdl_enter();
     JRL_CELL_PROLOGUE
     const float *s = f + b * 9 * g.HW + i;
     float *o = f_out + b * 9 * g.HW + i;
@@ -302,6 +305,7 @@ __global__ void __launch_bounds__(kThreads) k_wall(Grid g, WallParams p, const f
                                                    float *__restrict__ f_new, const float *__restrict__ phi,
                                                    const float *__restrict__ obs_vel)
 {
+    pdl_enter();
     JRL_CELL_PROLOGUE
     const float *s = f + b * 9 * g.HW + i;
     float *o = f_new + b * 9 * g.HW + i;
@@ -338,6 +342,10 @@ __device__ __forceinline__ void strip_terms(const float *__restrict__ C, const f
 __global__ void k_strip_flux(const float *__restrict__ C, const float *__restrict__ mesh, int y0, int ncol, int W,
                              float *__restrict__ out2)
 {
+    pdl_enter();
+    // block k = strip y0 + k (the walk loop records two adjacent strips per step in one launch)
+    y0 += blockIdx.x;
+    out2 += 2 * blockIdx.x;
 #ifdef JRL_HOST_EMU
     // one host "thread" plays the 32 lanes and the same xor tree, so the bits equal the GPU's
     float fl[32], pl[32];
@@ -438,6 +446,7 @@ __global__ void __launch_bounds__(kThreads) k_momentum_exchange(Grid g, const fl
 //      to fp32), so the fields equal the demo's bit for bit.
 __global__ void __launch_bounds__(kThreads) k_tip_conc(jrl_tip_desc d)
 {
+    pdl_enter();
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long HW = (long long)d.H * d.W;
     if (i >= HW)
@@ -486,6 +495,7 @@ __global__ void __launch_bounds__(kThreads) k_tip_conc(jrl_tip_desc d)
 // launch -- CalculateObsPhi (:39-49), the wall velocity field, and the OBSTACLE / velocity stamps inside the tip.
 __global__ void __launch_bounds__(kThreads) k_tip_fluid(jrl_tip_fluid_desc d)
 {
+    pdl_enter();
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long HW = (long long)d.H * d.W;
     if (i >= HW)
@@ -606,9 +616,9 @@ int jrl_stream_f32(const uint8_t *flags, const float *f, const float *phi_obs, f
     in.density = (float)inflow_density;
     cudaStream_t s = (cudaStream_t)stream;
     if (phi_obs)
-        JRL_LAUNCH(k_stream<true>, cell_grid(g, B), kThreads, s, g, flags, f, phi_obs, f_new, in);
+        JRL_LAUNCH_PDL(k_stream<true>, cell_grid(g, B), kThreads, s, g, flags, f, phi_obs, f_new, in);
     else
-        JRL_LAUNCH(k_stream<false>, cell_grid(g, B), kThreads, s, g, flags, f, nullptr, f_new, in);
+        JRL_LAUNCH_PDL(k_stream<false>, cell_grid(g, B), kThreads, s, g, flags, f, nullptr, f_new, in);
     return check_launch(fn);
 }
 
@@ -632,7 +642,7 @@ int jrl_moments_f32(const float *f, const float *rho_old, const float *vel_old, 
     JRL_REQUIRE(!use_contact || (H >= 4 && W >= 4), fn, "contact-angle wall density needs H, W >= 4");
     const Grid g = make_grid(H, W, 0);
     cudaStream_t s = (cudaStream_t)stream;
-    JRL_LAUNCH(k_moments<0>, cell_grid(g, B), kThreads, s, g, f, rho_old, vel_old, flags, rho_new, vel_new, use_contact, (float)c);
+    JRL_LAUNCH_PDL(k_moments<0>, cell_grid(g, B), kThreads, s, g, f, rho_old, vel_old, flags, rho_new, vel_new, use_contact, (float)c);
     if (use_contact)
     {
         const int ring = 2 * (H + W) - 4;
@@ -648,7 +658,7 @@ int jrl_moments_kernel_f32(const float *f, const float *rho_old, const float *ve
     JRL_REQUIRE(f && rho_old && vel_old && flags && rho_new && vel_new, fn, "null pointer");
     JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
     const Grid g = make_grid(H, W, 0);
-    JRL_LAUNCH(k_moments<1>, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, f, rho_old, vel_old, flags, rho_new, vel_new, 0, (float)c);
+    JRL_LAUNCH_PDL(k_moments<1>, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, f, rho_old, vel_old, flags, rho_new, vel_new, 0, (float)c);
     return check_launch(fn);
 }
 
@@ -730,7 +740,7 @@ int jrl_collide_f32(const jrl_collide_desc *d, void *stream)
     do                                                                                                        \
     {                                                                                                         \
         auto kern = k_collide<CONV, SRC>;                                                                     \
-        JRL_LAUNCH(kern, grid, kThreads, s, g, p, sp, d->f, d->rho, d->vel, d->flags, d->force, d->mesh_grid, \
+        JRL_LAUNCH_PDL(kern, grid, kThreads, s, g, p, sp, d->f, d->rho, d->vel, d->flags, d->force, d->mesh_grid, \
                    d->f_out);                                                                                 \
     } while (0)
     if (d->is_convection)
@@ -757,7 +767,7 @@ int jrl_wall_f32(double dt, double dx, double tau, const float *vel, const uint8
     JRL_REQUIRE(vel && flags && f && f_new && phi_obs, fn, "vel, flags, f, f_new, phi_obs required");
     JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
     const Grid g = make_grid(H, W, axisym);
-    JRL_LAUNCH(k_wall, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, make_wall(dt, dx, tau), vel, flags, f, f_new, phi_obs, obs_vel);
+    JRL_LAUNCH_PDL(k_wall, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, make_wall(dt, dx, tau), vel, flags, f, f_new, phi_obs, obs_vel);
     return check_launch(fn);
 }
 
@@ -766,12 +776,26 @@ int jrl_strip_flux_f32(const float *C, const float *mesh_grid, int y0, int ncol,
     const char *fn = "jrl_strip_flux_f32";
     JRL_REQUIRE(C && mesh_grid && out2, fn, "null pointer");
     JRL_REQUIRE(y0 >= 1 && y0 < H && ncol >= 1 && ncol + 1 <= W, fn, "strip outside the grid");
+    return jrl::strip_flux_n(C, mesh_grid, y0, 1, ncol, out2, H, W, stream);
+}
+
+extern "C++"
+{
+namespace jrl
+{
+int strip_flux_n(const float *C, const float *mesh_grid, int y0, int nstrips, int ncol, float *out2, int H, int W, void *stream)
+{
+    const char *fn = "jrl_strip_flux_f32";
+    JRL_REQUIRE(C && mesh_grid && out2, fn, "null pointer");
+    JRL_REQUIRE(nstrips >= 1 && y0 >= 1 && y0 + nstrips - 1 < H && ncol >= 1 && ncol + 1 <= W, fn, "strip outside the grid");
 #ifdef JRL_HOST_EMU
-    JRL_LAUNCH(k_strip_flux, 1, 1, (cudaStream_t)stream, C, mesh_grid, y0, ncol, W, out2);
+    JRL_LAUNCH(k_strip_flux, nstrips, 1, (cudaStream_t)stream, C, mesh_grid, y0, ncol, W, out2);
 #else
-    JRL_LAUNCH(k_strip_flux, 1, 32, (cudaStream_t)stream, C, mesh_grid, y0, ncol, W, out2);
+    JRL_LAUNCH_PDL(k_strip_flux, nstrips, 32, (cudaStream_t)stream, C, mesh_grid, y0, ncol, W, out2);
 #endif
     return check_launch(fn);
+}
+}  // namespace jrl
 }
 
 int jrl_momentum_exchange_f32(const float *f_post, const uint8_t *flags, double *out2, int B, int H, int W, void *stream)
@@ -796,7 +820,7 @@ int jrl_tip_prepare_conc_f32(const jrl_tip_desc *d, void *stream)
     JRL_REQUIRE(d->mesh_grid && d->flags && d->C && d->vel0 && d->phi_obs && d->C_vel, fn,
                 "mesh_grid, flags, C, vel0, phi_obs, C_vel required");
     JRL_REQUIRE(d->C_vel != d->vel0 && d->C_vel != d->vel1, fn, "C_vel must not alias the velocity snapshots");
-    JRL_LAUNCH(k_tip_conc, blocks_for((long long)d->H * d->W), kThreads, (cudaStream_t)stream, *d);
+    JRL_LAUNCH_PDL(k_tip_conc, blocks_for((long long)d->H * d->W), kThreads, (cudaStream_t)stream, *d);
     return check_launch(fn);
 }
 
@@ -806,7 +830,7 @@ int jrl_tip_prepare_fluid_f32(const jrl_tip_fluid_desc *d, void *stream)
     JRL_REQUIRE(d, fn, "null descriptor");
     JRL_REQUIRE(d->H >= 3 && d->W >= 3, fn, "H, W >= 3 required");
     JRL_REQUIRE(d->mesh_grid && d->flags && d->vel && d->phi_obs && d->obs_vel, fn, "mesh_grid, flags, vel, phi_obs, obs_vel required");
-    JRL_LAUNCH(k_tip_fluid, blocks_for((long long)d->H * d->W), kThreads, (cudaStream_t)stream, *d);
+    JRL_LAUNCH_PDL(k_tip_fluid, blocks_for((long long)d->H * d->W), kThreads, (cudaStream_t)stream, *d);
     return check_launch(fn);
 }
 
