@@ -6,8 +6,8 @@ and raises if it is missing, and every wrapper rejects tensors that are not CUDA
 `tensor.data_ptr()` and the stream is `torch.cuda.current_stream()`.
 
 (The CPU test-suite exercises the same kernel SOURCES compiled for the host by
-tests/host_emu/build.sh; it installs that library through `_install_test_library`, which is
-never called by product code.)
+tests/host_emu/build.sh; tests/host_emu/install.py monkeypatches this module from the outside to do
+so.  Nothing in this package knows about that library.)
 """
 from __future__ import annotations
 
@@ -21,7 +21,6 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libjrl_lbm.so")
 
 _lib = None
-_allow_cpu_tensors = False  # flipped only by _install_test_library (tests/host_emu)
 
 AXI_NOT, AXI_X, AXI_Y = 0, 1, 2
 OP_BGK, OP_MRT, OP_KBC = 0, 1, 2
@@ -122,14 +121,9 @@ def load():
     return _lib
 
 
-def _install_test_library(path):
-    """TESTS ONLY: route calls to the host-compiled build of the same kernel sources
-    (tests/host_emu/libjrl_lbm_emu.so) and accept CPU tensors.  Pass None to undo."""
-    global _lib, _allow_cpu_tensors
-    if path is None:
-        _lib, _allow_cpu_tensors = None, False
-    else:
-        _lib, _allow_cpu_tensors = _bind(ctypes.CDLL(path)), True
+def _require_cuda(t, name):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name}: tensor is on {t.device}; JRL-LBM-B200 has no CPU path (CUDA tensors only)")
 
 
 def stream_ptr(like: torch.Tensor):
@@ -155,8 +149,7 @@ def tensor_ptr(t, name, dtype=torch.float32, shape=None, like=None, optional=Fal
         raise RuntimeError(f"{name}: expected a torch.Tensor, got {type(t).__name__}")
     if t.dtype != dtype:
         raise RuntimeError(f"{name}: dtype {t.dtype} not supported, expected {dtype} (fp32 path only)")
-    if not t.is_cuda and not _allow_cpu_tensors:
-        raise RuntimeError(f"{name}: tensor is on {t.device}; JRL-LBM-B200 has no CPU path (CUDA tensors only)")
+    _require_cuda(t, name)
     if like is not None and t.device != like.device:
         raise RuntimeError(f"{name}: device {t.device} differs from {like.device}")
     if not t.is_contiguous():

@@ -39,7 +39,7 @@ def main():
     # jrl-lbm_b200/ must NOT be on sys.path here: its `src` package (the drop-in) would shadow
     # the reference's `src` namespace package.  Load the scenario builders by file path.
     import importlib.util
-    spec = importlib.util.spec_from_file_location("jrl_scenarios", os.path.join(ROOT, "jrl-lbm_b200", "jrl_scenarios.py"))
+    spec = importlib.util.spec_from_file_location("jrl_scenarios", os.path.join(ROOT, "tests", "jrl_scenarios.py"))
     S = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(S)
     from golden_cases import CASES

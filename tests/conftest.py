@@ -56,19 +56,18 @@ def emu_api():
     host logic and the kernel logic where no GPU exists.  Never used by -m gpu tests."""
     if have_cuda():
         pytest.skip("host emulation is for the CPU-only container; on a GPU box the CUDA library is tested")
-    import jrl_native
-    jrl_native._install_test_library(build_emu())
+    from host_emu import install as emu_install
+    emu_install.install(build_emu())
     import jrl_scenarios
     api = jrl_scenarios.api_from_src()
     yield api
-    jrl_native._install_test_library(None)
+    emu_install.uninstall()
 
 
 @pytest.fixture(scope="session")
 def cuda_api():
     """The product on the real library (libjrl_lbm.so, sm_100a).  Fails loudly if it is missing."""
     import jrl_native
-    jrl_native._install_test_library(None)
     jrl_native.load()
     import jrl_scenarios
     return jrl_scenarios.api_from_src()

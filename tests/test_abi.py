@@ -88,8 +88,9 @@ def test_no_cpu_fallback():
     """Product code path on a machine without CUDA: the Python layer refuses CPU tensors and the
     C entry point itself returns JRL_ERR_CUDA -- nothing computes on the host."""
     import jrl_native
-    saved = (jrl_native._lib, jrl_native._allow_cpu_tensors)  # the session-scoped emu_api fixture may be live
-    jrl_native._install_test_library(None)
+    saved = (jrl_native._lib, jrl_native._require_cuda)  # the session-scoped emu_api fixture may be live
+    from host_emu import install as emu_install
+    jrl_native._lib, jrl_native._require_cuda = None, emu_install._saved.get("req", jrl_native._require_cuda)
     try:
         jrl_native.load()
         import jrl_scenarios
@@ -110,4 +111,4 @@ def test_no_cpu_fallback():
         assert rc == -2, rc  # JRL_ERR_CUDA
         assert lib.jrl_last_error()
     finally:
-        jrl_native._lib, jrl_native._allow_cpu_tensors = saved
+        jrl_native._lib, jrl_native._require_cuda = saved

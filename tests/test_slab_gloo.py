@@ -17,8 +17,9 @@ H, W, STEPS = 30, 24, 9
 
 def _setup():
     sys.path.insert(0, PKG)
-    import jrl_native
-    jrl_native._install_test_library(build_emu())
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "host_emu"))
+    import install as emu_install
+    emu_install.install(build_emu())
     import jrl_scenarios as S
     return S, S.api_from_src()
 

@@ -2,7 +2,7 @@
 """Experiment: where does the time of the scaled C4 concentration step (8192^2) go?"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200")); sys.path.insert(1, os.path.join(ROOT, "tools"))
+sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200")); sys.path.append(os.path.join(ROOT, "tests"))  # tests/jrl_scenarios.py: the demo loop bodies; sys.path.insert(1, os.path.join(ROOT, "tools"))
 import torch
 import jrl_native
 jrl_native.load()

@@ -2,7 +2,7 @@
 """Experiment: where does the time of the C3 (cylinder, 800 x 400) fused step go?"""
 import os, sys, math
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200"))
+sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200")); sys.path.append(os.path.join(ROOT, "tests"))  # tests/jrl_scenarios.py: the demo loop bodies
 import torch
 import jrl_native
 jrl_native.load()

@@ -2,7 +2,7 @@
 """Experiment: small-grid BGK step time (jrl_run_f32) for builds of the library given on the command line."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200"))
+sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200")); sys.path.append(os.path.join(ROOT, "tests"))  # tests/jrl_scenarios.py: the demo loop bodies
 import torch
 import jrl_native
 def run(lib):

@@ -3,7 +3,7 @@
 for per-launch device times (C1/C2 at 130 x 130, C3 at 800 x 400, fused step via jrl_run_f32)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200"))
+sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200")); sys.path.append(os.path.join(ROOT, "tests"))  # tests/jrl_scenarios.py: the demo loop bodies
 import torch
 import jrl_native
 jrl_native.load()
