@@ -7,14 +7,15 @@
 // path compute bit-identical results.
 //
 // Arithmetic contract: fp32 storage; every expression keeps the operation ORDER of the
-// reference's path (cited per function, paths relative to the reference tree) and fp64
-// intermediates exactly where the reference's C++ literals force them.  The library is built
-// with -fmad=false, so the only fused multiply-adds are the ones written as fmaf() here.
+// reference's path AS IT RUNS ON CUDA (cited per function, paths relative to the reference tree):
+// fp64 intermediates exactly where the reference's C++ literals force them; torch's CUDA
+// semantics for the torch-op parts (division by a python scalar = multiplication by the fp32
+// reciprocal; `sum(dim=1)` = four interleaved accumulators; the batched 9x9 mat-vec = two FMA
+// chains) -- each measured against the reference-as-run on a B200 (tools/bench_ref_cuda.py).
+// The library is built with -fmad=false, so the only fused multiply-adds are the ones written
+// as fmaf() here.
 #pragma once
 #include <cstdint>
-#ifndef JRL_MRT_FMA
-#define JRL_MRT_FMA 1  // the 9x9 MRT matvec as 81 fmaf() (torch evaluates it as a GEMM, so no operation order is pinned; 0: separate mul + add)
-#endif
 #include <cuda_runtime.h>
 
 namespace jrl {
@@ -320,22 +321,34 @@ __device__ __forceinline__ void stream_cell(const Grid &g, const float *__restri
 }
 
 // ------------------------------------------------------------------------------------------
-// R2 / R7: moments (LBM_macro_compute_2d.py:316-351, 273-295).  Sequential fp32 sums, q = 0..8.
+// R2 / R7: moments (LBM_macro_compute_2d.py:316-351, 273-295).
+// The reference evaluates `f.sum(dim=1)` and `(f.unsqueeze(2) * e).sum(1)` with torch on CUDA (it hard-requires
+// CUDA, readme.md:7).  ATen's reduction kernel gives every output its own thread there (9 inputs per output, far
+// below the split threshold) and that thread keeps vt0 = 4 interleaved accumulators, element k into accumulator
+// k % 4, combined in order at the end (ATen/native/cuda/Reduce.cuh, thread_reduce_impl):
+//     ((((a0 + a4) + a8) + (a1 + a5)) + (a2 + a6)) + (a3 + a7)
+// Established on a B200 against the reference-as-run (tools/bench_ref_cuda.py, tools/exp_torch_order.py: 0 differing
+// bits in rho, u, C over every golden case) and pinned by tests/golden/refcuda_*.npz.
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float torch_sum9(float a0, float a1, float a2, float a3, float a4, float a5, float a6,
+                                            float a7, float a8)
+{
+    return ((((a0 + a4) + a8) + (a1 + a5)) + (a2 + a6)) + (a3 + a7);
+}
+
 __device__ __forceinline__ float sum9(const float f[9])
 {
-    float s = f[0];
-#pragma unroll
-    for (int q = 1; q < 9; ++q)
-        s = s + f[q];
-    return s;
+    return torch_sum9(f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7], f[8]);
 }
 
 __device__ __forceinline__ void momentum9(const float f[9], float &mx, float &my)
 {
-    // sum_q f_q e_q accumulated in direction order; terms with e = 0 add +-0 and are skipped
-    mx = ((((f[1] - f[3]) + f[5]) - f[6]) - f[7]) + f[8];
-    my = ((((f[2] - f[4]) + f[5]) + f[6]) - f[7]) - f[8];
+    // sum_q f_q e_q in the same accumulator order; e is 0 or +-1, so the products are exact and the zero terms
+    // (which only add +-0 to an accumulator) are dropped:
+    //   x: acc0 = f8, acc1 = f1 + f5, acc2 = -f6, acc3 = -(f3 + f7)
+    //   y: acc0 = -(f4 + f8), acc1 = f5, acc2 = f2 + f6, acc3 = -f7
+    mx = ((f[8] + (f[1] + f[5])) - f[6]) - (f[3] + f[7]);
+    my = ((f[5] - (f[4] + f[8])) + (f[2] + f[6])) - f[7];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -406,6 +419,22 @@ struct CollideParams
     float mrt[81];   // M^-1 S M, row-major (LBM_collision_MRT_2d.py:59-69), built on the host
 };
 
+// One row of a torch-CUDA batched 9x9 mat-vec (`mat @ x.unsqueeze(-1)`, LBM_collision_MRT_2d.py:97-100,
+// LBM_collision_KBC_2d.py:107-130): cuBLAS's kernel for this shape accumulates k = 0..4 and k = 5..8 as two FMA
+// chains starting from 0 and adds the two halves.  Identified on a B200 by tools/exp_torch_order.py (0 differing bits
+// over 10^5 products, shared and per-cell matrices, batch 1 and 2) and pinned by tests/golden/refcuda_*.npz.
+__device__ __forceinline__ float dot9_cublas(const float *a, const float *x)
+{
+    float lo = 0.f, hi = 0.f;
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+        lo = fmaf(a[k], x[k], lo);
+#pragma unroll
+    for (int k = 5; k < 9; ++k)
+        hi = fmaf(a[k], x[k], hi);
+    return lo + hi;
+}
+
 // Entropic KBC relaxation, LBM_collision_KBC_2d.py:70-249.  Returns Omega in om[].
 __device__ __forceinline__ void kbc_omega(const CollideParams &p, float rho, float ux, float uy,
                                           const float f[9], const float feq[9], float om[9])
@@ -420,32 +449,37 @@ __device__ __forceinline__ void kbc_omega(const CollideParams &p, float rho, flo
         return;
     }
     const bool central = (type == KBC_A || type == KBC_B);
-    // second-order moments M20, M11, M02 of f and feq
-    float m20 = 0.f, m11 = 0.f, m02 = 0.f, q20 = 0.f, q11 = 0.f, q02 = 0.f;
-#pragma unroll
-    for (int q = 0; q < 9; ++q)
+    // second-order moments M20, M11, M02 of f and feq: rows 3, 4, 5 of `C_mat @ f` / `euev @ f` (:100-130), a batched
+    // 9x9 mat-vec that torch-CUDA hands to cuBLAS, whose kernel sums k = 0..4 and k = 5..8 as two FMA chains and adds
+    // the halves (matvec9 below; tools/exp_torch_order.py).  With raw moments the coefficients are 0 / +-1 and the
+    // FMAs reduce to exact adds.
+    float m20, m11, m02, q20, q11, q02;
     {
-        float a20, a11, a02;
-        if (central)
+        float a20[9], a11[9], a02[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q)
         {
-            const float dxm = (float)JRL_EX(q) - ux;  // (c e - u), c = 1 (:96-105)
-            const float dym = (float)JRL_EY(q) - uy;
-            a20 = (dxm * dxm) * 1.f;
-            a11 = dxm * dym;
-            a02 = 1.f * (dym * dym);
+            if (central)
+            {
+                const float dxm = (float)JRL_EX(q) - ux;  // (c e - u), c = 1 (:96-105)
+                const float dym = (float)JRL_EY(q) - uy;
+                a20[q] = (dxm * dxm) * 1.f;
+                a11[q] = dxm * dym;
+                a02[q] = 1.f * (dym * dym);
+            }
+            else
+            {
+                a20[q] = (float)(JRL_EX(q) * JRL_EX(q));
+                a11[q] = (float)(JRL_EX(q) * JRL_EY(q));
+                a02[q] = (float)(JRL_EY(q) * JRL_EY(q));
+            }
         }
-        else
-        {
-            a20 = (float)(JRL_EX(q) * JRL_EX(q));
-            a11 = (float)(JRL_EX(q) * JRL_EY(q));
-            a02 = (float)(JRL_EY(q) * JRL_EY(q));
-        }
-        m20 = m20 + a20 * f[q];
-        m11 = m11 + a11 * f[q];
-        m02 = m02 + a02 * f[q];
-        q20 = q20 + a20 * feq[q];
-        q11 = q11 + a11 * feq[q];
-        q02 = q02 + a02 * feq[q];
+        m20 = dot9_cublas(a20, f);
+        m11 = dot9_cublas(a11, f);
+        m02 = dot9_cublas(a02, f);
+        q20 = dot9_cublas(a20, feq);
+        q11 = dot9_cublas(a11, feq);
+        q02 = dot9_cublas(a02, feq);
     }
     const float T = m20 + m02, N = m20 - m02, P = m11;
     const float Te = q20 + q02, Ne = q20 - q02, Pe = q11;
@@ -485,19 +519,17 @@ __device__ __forceinline__ void kbc_omega(const CollideParams &p, float rho, flo
     se[7] = 0.25f * Pe;
     se[8] = 0.25f * (-Pe);
     const float eps = 1e-10f;
-    float ds[9], dh[9];
-    float dsdh = 0.f, dhdh = 0.f;
+    float ds[9], dh[9], a[9], b[9];
 #pragma unroll
     for (int q = 0; q < 9; ++q)
     {
         ds[q] = s[q] - se[q];
         dh[q] = (f[q] - feq[q]) - ds[q];
         const float den = feq[q] + eps;
-        const float a = (ds[q] * dh[q]) / den;
-        const float b = (dh[q] * dh[q]) / den;
-        dsdh = q == 0 ? a : dsdh + a;
-        dhdh = q == 0 ? b : dhdh + b;
+        a[q] = (ds[q] * dh[q]) / den;
+        b[q] = (dh[q] * dh[q]) / den;
     }
+    const float dsdh = sum9(a), dhdh = sum9(b);  // `.sum(dim=1, keepdim=True)` (:240-241): torch-CUDA order
     const float gamma = p.inv_beta - p.two_m_inv_beta * (dsdh / (dhdh + eps));
 #pragma unroll
     for (int q = 0; q < 9; ++q)
@@ -571,17 +603,7 @@ __device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, 
             d[q] = feq[q] - f[q];
 #pragma unroll
         for (int i = 0; i < 9; ++i)
-        {
-            float acc = 0.f;
-#pragma unroll
-            for (int j = 0; j < 9; ++j)
-#if JRL_MRT_FMA
-                acc = fmaf(p.mrt[i * 9 + j], d[j], acc);
-#else
-                acc = acc + p.mrt[i * 9 + j] * d[j];
-#endif
-            om[i] = acc;
-        }
+            om[i] = dot9_cublas(p.mrt + i * 9, d);
     }
     else
         kbc_omega(p, rho, ux_raw, uy_raw, f, feq, om);

@@ -212,14 +212,17 @@ _MRT_M = [
 ]  # Lallemand-Luo moment basis in this lattice's direction order, LBM_collision_MRT_2d.py:41-57
 
 
-def mrt_operator(tau):
+def mrt_operator(tau, device="cpu"):
     """M^-1 S M as a host fp32 [9,9] tensor, S = diag(0, s7, s7, 0, s4, 0, s4, s7, s7), s7 = 1/tau,
-    s4 = 8(2 - s7)/(8 - s7)  (LBM_collision_MRT_2d.py:59-69).  Built once per preset_KBC."""
-    M = torch.tensor(_MRT_M, dtype=torch.float32)
+    s4 = 8(2 - s7)/(8 - s7)  (LBM_collision_MRT_2d.py:36-69).  Built once per preset_KBC with the reference's own
+    torch calls ON THE RUN'S DEVICE -- `torch.linalg.inv` and the 9x9 product give different last bits on CUDA
+    (cuSOLVER / cuBLAS) and on the CPU (LAPACK), and the kernels multiply by exactly this matrix -- then copied to
+    the host once (the C ABI takes the 81 coefficients by host pointer)."""
+    M = torch.Tensor(_MRT_M).to(torch.float32).to(device).reshape(1, 1, 1, 9, 9)
     s7 = 1.0 / tau
     s4 = 8.0 * (2 - s7) / (8 - s7)
-    S = torch.tensor([0.0, s7, s7, 0.0, s4, 0.0, s4, s7, s7], dtype=torch.float32).reshape(9, 1)
-    return (torch.linalg.inv(M) @ (S * M)).contiguous()
+    S = torch.Tensor([0.0, s7, s7, 0.0, s4, 0.0, s4, s7, s7]).to(torch.float32).to(device).reshape(1, 1, 1, 9, 1)
+    return (torch.linalg.inv(M) @ (S * M)).reshape(9, 9).to("cpu").contiguous()
 
 
 class LBMCollision2d:
@@ -326,7 +329,7 @@ class LBMCollisionMRT2d(LBMCollision2d):
 
     def preset_KBC(self, dx, dt, tau, tau_D=None):
         self._tau = tau
-        self._mrt = mrt_operator(tau)
+        self._mrt = mrt_operator(tau, self.device)
         self.Minv_S_M = self._mrt.reshape(1, 1, 1, 9, 9).to(self.device)
         if tau_D is not None:
             self._tau_D = tau_D

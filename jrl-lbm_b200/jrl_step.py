@@ -45,7 +45,7 @@ class FusedStep:
                 raise RuntimeError("is_convection needs tau_D")
             self.tau = float(tau_D)
         self.dx, self.dt = float(dx), float(dt)
-        self._mrt = mrt_operator(self.tau) if self.op == N.OP_MRT else None
+        self._mrt = mrt_operator(self.tau, parameters.device) if self.op == N.OP_MRT else None
         ca = parameters.contact_angle if isinstance(contact_angle, str) else contact_angle
         self.use_contact = (ca is not None) and not self.is_convection
         if self.use_contact:

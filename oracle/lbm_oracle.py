@@ -14,6 +14,13 @@ so the pins are outputs of the reference itself run in the build container:
     axisymmetric source) is checked against tests/golden/*.npz, written by
     oracle/gen_golden.py from the reference's unmodified Python classes imported on the CPU
     (oracle/ref_cpu.py) -- tests/test_oracle_golden.py.
+  * the torch-op paths follow torch's CUDA arithmetic, because the reference hard-requires CUDA
+    (readme.md:7): division by a python scalar = multiplication by the fp32 reciprocal, `sum(dim=1)`
+    = four interleaved accumulators, batched 9x9 mat-vec = two FMA chains (`_sum9`, `_matvec9`).
+    Those orders were measured on a B200 against the reference-as-run (tools/bench_ref_cuda.py,
+    tools/exp_torch_order.py) and are pinned by tests/golden/refcuda_*.npz = outputs of the
+    reference's own fast-math CUDA build -- tests/test_oracle_golden.py::test_oracle_vs_refcuda.
+    (The CPU-torch fixtures above differ from them in the last bit; the 1e-5 bar covers both.)
 One documented deviation: OUTFLOW cells (propagation.cu:195-255) read a neighbour's f_new
 that another CUDA thread writes in the same launch (a data race).  The oracle, like the new
 kernels, defines the result as "the neighbour's value after streaming and inflow reset".
@@ -379,11 +386,30 @@ def contact_angle_correctness(rho, flags, contact_angle):
 
 
 def _sum9(f):
-    """Sequential sum over the direction axis (fp32, q = 0..8 in order)."""
-    s = f[:, 0].copy()
-    for q in range(1, 9):
-        s = s + f[:, q]
-    return s[:, None]
+    """`t.sum(dim=1, keepdim=True)` as torch evaluates it on CUDA for a 9-long reduction: one thread per output,
+    vt0 = 4 interleaved accumulators (element k into accumulator k % 4), combined in order
+    (ATen/native/cuda/Reduce.cuh thread_reduce_impl): ((((a0+a4)+a8) + (a1+a5)) + (a2+a6)) + (a3+a7)."""
+    a = [f[:, q] for q in range(9)]
+    s = (((a[0] + a[4]) + a[8]) + (a[1] + a[5])) + (a[2] + a[6])
+    return (s + (a[3] + a[7]))[:, None]
+
+
+def _fma(a, b, c):
+    """fmaf(a, b, c) for float32 arrays: the product is exact in float64; the sum is rounded to float64 and then
+    to float32 (double rounding differs from a true FMA with probability ~2^-29 per operation)."""
+    return (np.asarray(a, F64) * np.asarray(b, F64) + np.asarray(c, F64)).astype(F32)
+
+
+def _dot9(coef, x):
+    """One row of torch-CUDA's batched 9x9 mat-vec: k = 0..4 and k = 5..8 as two FMA chains from 0, halves added
+    (cuBLAS kernel for this shape; measured by tools/exp_torch_order.py).  coef: 9 scalars or per-cell arrays."""
+    lo = np.zeros_like(x[:, 0])
+    hi = np.zeros_like(x[:, 0])
+    for k in range(5):
+        lo = _fma(coef[k], x[:, k], lo)
+    for k in range(5, 9):
+        hi = _fma(coef[k], x[:, k], hi)
+    return lo + hi
 
 
 def macro_compute(dx, dt, f, rho, vel, flags, contact_angle=None):
@@ -393,11 +419,8 @@ def macro_compute(dx, dt, f, rho, vel, flags, contact_angle=None):
     rho_new = np.where(obs, rho, _sum9(f))
     if contact_angle is not None:
         rho_new = contact_angle_correctness(rho_new, flags, contact_angle)
-    mx = np.zeros_like(f[:, 0])
-    my = np.zeros_like(f[:, 0])
-    for q in range(9):
-        mx = mx + f[:, q] * F32(E[q, 0])
-        my = my + f[:, q] * F32(E[q, 1])
+    mx = _sum9(f * E[:, 0].astype(F32).reshape(1, 9, 1, 1))[:, 0]      # (f.unsqueeze(2) * e).sum(1), :335
+    my = _sum9(f * E[:, 1].astype(F32).reshape(1, 9, 1, 1))[:, 0]
     with np.errstate(divide="ignore", invalid="ignore"):
         inv = F32(c) / rho_new
         vel_new = np.stack([mx, my], axis=1) * inv
@@ -570,10 +593,7 @@ def collide_mrt(dx, dt, f, rho, vel, flags, tau, force=None, mesh_grid=None, axi
     d = feq - f
     omega = np.zeros_like(f)
     for i in range(9):
-        acc = np.zeros_like(f[:, 0])
-        for j in range(9):
-            acc = acc + mat[i, j] * d[:, j]
-        omega[:, i] = acc
+        omega[:, i] = _dot9(mat[i], d)
     Gi = axisym_source(dx, dt, rho, vel, flags, feq, tau, axisym, False, mesh_grid)
     out = f + omega + dt * Gi
     return np.where(flags == OBSTACLE, f, out).astype(F32)
@@ -601,16 +621,10 @@ def kbc_omega(rho, vel, f, feq, tau, kbc_type):
         dym = [F32(E[q, 1]) - vel[:, 1] for q in range(9)]
 
         def mom(g, k):
-            acc = np.zeros_like(g[:, 0])
-            for q in range(9):
-                acc = acc + (dxm[q] ** KBC_P[k]) * (dym[q] ** KBC_Q[k]) * g[:, q]
-            return acc[:, None]
+            return _dot9([(dxm[q] ** KBC_P[k]) * (dym[q] ** KBC_Q[k]) for q in range(9)], g)[:, None]
     else:
         def mom(g, k):
-            acc = np.zeros_like(g[:, 0])
-            for q in range(9):
-                acc = acc + KBC_CMAT[k, q] * g[:, q]
-            return acc[:, None]
+            return _dot9(KBC_CMAT[k], g)[:, None]
     M20, M11, M02 = mom(f, 3), mom(f, 4), mom(f, 5)
     Q20, Q11, Q02 = mom(feq, 3), mom(feq, 4), mom(feq, 5)
     T, N, P = M20 + M02, M20 - M02, M11

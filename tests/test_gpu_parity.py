@@ -27,7 +27,7 @@ def dev():
 def test_case_matches_reference_golden(cuda_api, dev, name):
     fn, kw = CASES[name]
     got = getattr(S, fn)(cuda_api, dev, **kw)
-    compare_outputs(got, load_golden(name))
+    compare_outputs(got, load_golden(name), case=name)
 
 
 @pytest.mark.parametrize("name", list(CASES))
@@ -49,7 +49,7 @@ def test_fused_matches_reference_golden(cuda_api, dev, name):
     fn, kw = CASES[name]
     got = getattr(S, fn)(cuda_api, dev, fused=True, **kw)
     skip = [k for k in load_golden(name) if k.startswith("snap_")]
-    compare_outputs(got, load_golden(name), skip=skip)
+    compare_outputs(got, load_golden(name), skip=skip, case=name)
 
 
 def test_large_grid_fused_equals_chain_and_conserves_mass(cuda_api, dev):

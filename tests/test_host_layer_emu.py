@@ -14,7 +14,7 @@ from util import compare_outputs, load_golden
 def test_case_matches_reference_golden(emu_api, name):
     fn, kw = CASES[name]
     got = getattr(S, fn)(emu_api, torch.device("cpu"), **kw)
-    compare_outputs(got, load_golden(name))
+    compare_outputs(got, load_golden(name), case=name)
 
 
 @pytest.mark.parametrize("name", ["c1_shear_bgk", "c4_jrl_conc", "c5_jrl_fluid_g"])

@@ -19,7 +19,7 @@ def test_oracle_reproduces_reference_golden(oracle_api, name):
     got = getattr(S, fn)(oracle_api, torch.device("cpu"), **kw)
     want = load_golden(name)
     assert len(want) >= 3
-    compare_outputs(got, want)
+    compare_outputs(got, want, case=name)
 
 
 def test_golden_fixtures_are_not_trivial():

@@ -9,6 +9,23 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 # steps in fp32"; masks and indexing bit-exact.
 REL_L2_TOL = 1e-5
 
+# One field needs a wider bar: the velocity of the axisymmetric stage-A flow.  |u| ~ 1e-3 is the difference of populations ~ 0.1-0.4, so its fp32 noise floor is ~1e-5 relative, and
+# the REFERENCE ITSELF does not reproduce it across devices: its CPU-torch run and its CUDA run (as shipped,
+# --use_fast_math) of c5_jrl_fluid_g differ by 1.4e-5 in `vel` after 80 steps (rho, f: 1e-7), measured on a B200 with
+# tools/bench_ref_cuda.py (profiles/r2_refcuda_summary.json).  This library follows the CUDA arithmetic (the reference
+# hard-requires CUDA): its torch-op parts match the CUDA fixtures (tests/golden/refcuda_*) to the last bit; what is left
+# is the FMA contraction / fast-math division of the reference's streaming and moving-wall kernels (~1e-9 per call in
+# f), which the same cancellation amplifies to ~1e-5 in u.
+STAGE_A_VEL_TOL = 5e-5
+
+
+def field_tol(case, key, tol=REL_L2_TOL):
+    """Relative-L2 bar for `key` of golden case `case` (1e-5 everywhere except the stage-A velocity)."""
+    if "jrl_fluid" in case or case.startswith("a_"):
+        if "vel" in key:
+            return STAGE_A_VEL_TOL
+    return tol
+
 
 def rel_l2(a, b):
     a = np.asarray(a, np.float64).ravel()
@@ -24,9 +41,9 @@ def load_golden(name):
         return {k: z[k] for k in z.files}
 
 
-def compare_outputs(got, want, tol=REL_L2_TOL, skip=()):
-    """Every key of `want`: integer arrays bit-exact, float arrays within `tol` relative L2,
-    python scalars to 1e-12.  Returns {key: rel_l2} for reporting."""
+def compare_outputs(got, want, tol=REL_L2_TOL, skip=(), case=""):
+    """Every key of `want`: integer arrays bit-exact, float arrays within `tol` relative L2 (see field_tol
+    for the one widened field), python scalars to 1e-12.  Returns {key: rel_l2} for reporting."""
     report = {}
     for k, w in want.items():
         if k in skip:
@@ -45,5 +62,6 @@ def compare_outputs(got, want, tol=REL_L2_TOL, skip=()):
             assert g.shape == w.shape, f"{k}: shape {g.shape} vs {w.shape}"
             e = rel_l2(g, w)
             report[k] = e
-            assert e <= tol, f"{k}: relative L2 {e:.3e} > {tol:g}"
+            t = field_tol(case, k, tol)
+            assert e <= t, f"{k}: relative L2 {e:.3e} > {t:g}"
     return report
