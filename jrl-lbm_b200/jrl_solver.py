@@ -3,9 +3,12 @@
 Same class names, method names, keyword names, return arity and in-place side effects as the
 reference (every method cites the reference method it replaces, paths
 relative to the reference tree), so demo/*.py and batch_validation.py drive it unchanged.
-Each method is ONE library launch (the reference: one custom kernel plus 10-80 torch
-elementwise launches and one or two full copies of f).  The fused single-launch step and the
-multi-GPU row-slab driver live in jrl_step.py / jrl_slab.py.
+Each method is at most ONE library launch (the reference: one custom kernel plus 10-80 torch
+elementwise launches and one or two full copies of f) -- and when a demo calls them in the
+reference's order, propagation -> [solve_boundary] -> macro_compute(_C) -> collision, the first
+three only record the call and collision() launches the whole step as ONE fused kernel
+(jrl_lazy.py; bit-identical to the four launches).  The explicit fused-step API and the multi-GPU
+row-slab driver live in jrl_step.py / jrl_slab.py.
 
 No CPU path: CUDA fp32 tensors only (uint8 flags); anything else raises RuntimeError.
 """
@@ -13,10 +16,13 @@ from __future__ import annotations
 
 import ctypes
 import math
+import weakref
 
 import torch
 
+import jrl_lazy as L
 import jrl_native as N
+from jrl_lazy import resolve
 
 CELL_OBSTACLE = 2
 CELL_INFLOW_2 = 32
@@ -28,6 +34,11 @@ def _dims(f, name="f"):
         raise RuntimeError(f"{name}: expected a [B,C,H,W] tensor")
     B, _, H, W = f.shape
     return int(B), int(H), int(W)
+
+
+def _opt(t):
+    """The reference passes `torch.Tensor([])` for an absent optional (propagation.cu:513-517)."""
+    return None if (t is None or t.numel() == 0) else t
 
 
 def _full(t, shape, name, like):
@@ -53,28 +64,52 @@ class LBMPropagation2d:
         self.axisymmetric_type = int(axisymmetric_type)
         self.device = device
         self.dtype = dtype
-        self._inflow2_cache = None  # (data_ptr, _version, shape) -> bool
+        self._inflow2_cache = None  # (weakref of the flags tensor, its _version) -> bool
 
     def _has_inflow2(self, flags):
         # LBM_propagation_2d.py:58 syncs the host every step with `(flags == INFLOW_2).any()`;
         # the answer only changes when `flags` is written, which bumps the tensor's version counter.
-        key = (flags.data_ptr(), flags._version, tuple(flags.shape))
-        if self._inflow2_cache is None or self._inflow2_cache[0] != key:
-            self._inflow2_cache = (key, bool((flags == CELL_INFLOW_2).any()))
-        return self._inflow2_cache[1]
+        # The entry is tied to the tensor OBJECT (weak reference), not to its address: the caching
+        # allocator hands a freed flags buffer of one run to the next run at the same address.
+        c = self._inflow2_cache
+        if c is None or c[0]() is not flags or c[1] != flags._version:
+            c = self._inflow2_cache = (weakref.ref(flags), flags._version, bool((flags == CELL_INFLOW_2).any()))
+        return c[2]
 
     def propagation(self, f, flags, phi_obs=None, rho=None, vel=None, inflow_vel=None, inflow_density=None,
                     is_convection=False):
-        """Pull streaming with every link rule; one launch of jrl_stream_f32.
-        Returns f_new, or (rho, vel, f_new) under the reference's rule (LBM_propagation_2d.py:52-59,
-        89-92); rho / vel are mutated in place at INFLOW / INFLOW_2 cells (propagation.cu:300-362)."""
+        """Pull streaming with every link rule (jrl_stream_f32) -- recorded, not launched, when the fused step may
+        follow (jrl_lazy.py).  Returns f_new, or (rho, vel, f_new) under the reference's rule
+        (LBM_propagation_2d.py:52-59, 89-92); rho / vel are mutated in place at INFLOW / INFLOW_2 cells
+        (propagation.cu:300-362) -- at the latest when anything looks at them."""
+        f, flags, phi_obs, rho, vel, inflow_vel = (resolve(t) for t in (f, flags, phi_obs, rho, vel, inflow_vel))
         B, H, W = _dims(f)
         inflow_info = inflow_density is not None or inflow_vel is not None
         if inflow_info:
             assert rho is not None
-        p_flags = N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f)
+        N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f)
         if not inflow_info:
             inflow_info = self._has_inflow2(flags)
+        if not (L.ENABLED and H >= 3 and W >= 3):
+            f_new = self._stream(f, flags, phi_obs, rho, vel, inflow_vel, inflow_density)
+            if inflow_info:
+                return (torch.Tensor([]) if rho is None else rho, torch.Tensor([]) if vel is None else vel, f_new)
+            return f_new
+        for t, name, shape in ((f, "f", (B, 9, H, W)), (phi_obs, "phi_obs", (B, 1, H, W)), (rho, "rho", (B, 1, H, W)),
+                               (vel, "vel", (B, 2, H, W)), (inflow_vel, "inflow_vel", (2,))):
+            N.tensor_ptr(t, name, shape=shape, like=f, optional=name != "f")  # validate now, as the eager call would
+        P = L.PendingStep(self, f, flags, _opt(phi_obs), _opt(rho), _opt(vel), _opt(inflow_vel), inflow_density)
+        f_new = P.handle("f_stream", f.shape, f)
+        if inflow_info:
+            r = torch.Tensor([]) if rho is None else (P.handle("rho_in", rho.shape, rho) if rho.numel() else rho)
+            v = torch.Tensor([]) if vel is None else (P.handle("vel_in", vel.shape, vel) if vel.numel() else vel)
+            return (r, v, f_new)
+        return f_new
+
+    def _stream(self, f, flags, phi_obs, rho, vel, inflow_vel, inflow_density):
+        """One launch of jrl_stream_f32 (K1, propagation.cu:22-488)."""
+        B, H, W = _dims(f)
+        p_flags = N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f)
         p_f = N.tensor_ptr(f, "f", shape=(B, 9, H, W))
         p_phi = N.tensor_ptr(phi_obs, "phi_obs", shape=(B, 1, H, W), like=f, optional=True)
         p_rho = N.tensor_ptr(rho, "rho", shape=(B, 1, H, W), like=f, optional=True)
@@ -83,12 +118,11 @@ class LBMPropagation2d:
         f_new = torch.empty_like(f)
         N.call("jrl_stream_f32", p_flags, p_f, p_phi, ctypes.c_void_p(f_new.data_ptr()), p_rho, p_vel, p_iv,
                -1.0 if inflow_density is None else float(inflow_density), self.axisymmetric_type, B, H, W, like=f)
-        if inflow_info:
-            return (torch.Tensor([]) if rho is None else rho, torch.Tensor([]) if vel is None else vel, f_new)
         return f_new
 
     def rebounce_obstacle(self, f, flags):
         """OBSTACLE cells get their populations reversed (LBM_propagation_2d.py:181-186)."""
+        f, flags = resolve(f), resolve(flags)
         B, H, W = _dims(f)
         f_new = torch.empty_like(f)
         N.call("jrl_rebounce_f32", N.tensor_ptr(f, "f", shape=(B, 9, H, W)),
@@ -137,7 +171,28 @@ class LBMMacroCompute2d:
     def macro_compute(self, dx, dt, f, rho, vel, flags, g=None, pressure=None, density=None):
         """rho = sum f, u = sum f e c / rho; OBSTACLE cells keep the old values, with the
         contact-angle wall density when contact_angle is not None (LBM_macro_compute_2d.py:316-351,
-        237-271).  One launch of jrl_moments_f32 (+ a ring kernel for the wall density)."""
+        237-271).  One launch of jrl_moments_f32 (+ a ring kernel for the wall density) -- recorded, not launched,
+        when `f` is the still-unlaunched result of propagation() [+ solve_boundary()] on the same flags."""
+        P = f.pending if isinstance(f, L.LazyField) else None
+        if (P is not None and density is None and P.moments is None and P.owns(f, P.f_role()) and flags is P.flags
+                and (P.rho_in is None or P.is_input(rho, P.rho_in, "rho_in"))
+                and (P.vel_in is None or P.is_input(vel, P.vel_in, "vel_in"))):
+            B, H, W = _dims(f)
+            rho_t = P.rho_in if P.rho_in is not None else resolve(rho)
+            vel_t = P.vel_in if P.vel_in is not None else resolve(vel)
+            N.tensor_ptr(rho_t, "rho", shape=(B, 1, H, W), like=P.f_in)
+            N.tensor_ptr(vel_t, "vel", shape=(B, 2, H, W), like=P.f_in)
+            return P.add_moments(self, "fluid", dx, dt, rho_t, vel_t)
+        f, rho, vel, flags = resolve(f), resolve(rho), resolve(vel), resolve(flags)
+        rho_new, vel_new = self._moments(dx, dt, f, rho, vel, flags)
+        if density is not None:
+            # multiphase density remap (LBM_macro_compute_2d.py:338-349); no demo takes this branch
+            density = self._density_gas + (self._density_liquid - self._density_gas) * (
+                (rho_new - self._rho_gas) / (self._rho_liquid - self._rho_gas))
+            return [rho_new, vel_new, density]
+        return [rho_new, vel_new]
+
+    def _moments(self, dx, dt, f, rho, vel, flags):
         B, H, W = _dims(f)
         rho_new = torch.empty((B, 1, H, W), dtype=f.dtype, device=f.device)
         vel_new = torch.empty((B, 2, H, W), dtype=f.dtype, device=f.device)
@@ -147,15 +202,19 @@ class LBMMacroCompute2d:
                N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f),
                ctypes.c_void_p(rho_new.data_ptr()), ctypes.c_void_p(vel_new.data_ptr()),
                int(use_contact), self._contact_tan() if use_contact else 0.0, float(dx) / float(dt), B, H, W, like=f)
-        if density is not None:
-            # multiphase density remap (LBM_macro_compute_2d.py:338-349); no demo takes this branch
-            density = self._density_gas + (self._density_liquid - self._density_gas) * (
-                (rho_new - self._rho_gas) / (self._rho_liquid - self._rho_gas))
-            return [rho_new, vel_new, density]
-        return [rho_new, vel_new]
+        return rho_new, vel_new
 
     def macro_compute_C(self, dx, dt, h, C, flags, vel, mesh_grid):
-        """C = sum h; OBSTACLE cells keep C (LBM_macro_compute_2d.py:273-295)."""
+        """C = sum h; OBSTACLE cells keep C (LBM_macro_compute_2d.py:273-295).  Recorded, not launched, when `h` is the
+        still-unlaunched result of propagation() on the same flags with `C` as its rho."""
+        P = h.pending if isinstance(h, L.LazyField) else None
+        if (P is not None and P.moments is None and P.wall is None and P.owns(h, "f_stream") and flags is P.flags
+                and P.rho_in is not None and P.is_input(C, P.rho_in, "rho_in")):
+            return P.add_moments(self, "C", dx, dt, P.rho_in, resolve(vel) if not P.is_input(vel, P.vel_in, "vel_in")
+                                 else P.vel_in, mesh_grid=mesh_grid)
+        return self._moments_C(resolve(h), resolve(C), resolve(flags))
+
+    def _moments_C(self, h, C, flags):
         B, H, W = _dims(h, "h")
         C_new = torch.empty((B, 1, H, W), dtype=h.dtype, device=h.device)
         N.call("jrl_moments_C_f32", N.tensor_ptr(h, "h", shape=(B, 9, H, W)),
@@ -166,6 +225,7 @@ class LBMMacroCompute2d:
 
     def ApplyCompute_C(self, dx, dt, h, C, flags, vel, mesh_grid):
         """The reference's CUDA twin with the axisymmetric division (macro_compute.cu:22-78)."""
+        h, C, flags, vel, mesh_grid = (resolve(t) for t in (h, C, flags, vel, mesh_grid))
         B, H, W = _dims(h, "h")
         C_new = torch.empty((B, 1, H, W), dtype=h.dtype, device=h.device)
         N.call("jrl_moments_C_kernel_f32", float(dt), N.tensor_ptr(h, "h", shape=(B, 9, H, W)),
@@ -178,6 +238,7 @@ class LBMMacroCompute2d:
 
     def ApplyCompute_fluid(self, dx, dt, f, rho, vel, flags, g=None, pressure=None, density=None):
         """Moments without the wall-density step (macro_compute.cu:80-157)."""
+        f, rho, vel, flags = resolve(f), resolve(rho), resolve(vel), resolve(flags)
         B, H, W = _dims(f)
         rho_new = torch.empty((B, 1, H, W), dtype=f.dtype, device=f.device)
         vel_new = torch.empty((B, 2, H, W), dtype=f.dtype, device=f.device)
@@ -191,6 +252,7 @@ class LBMMacroCompute2d:
     def get_vort(self, vel, dx):
         """Central-difference vorticity for the PNG dumps (LBM_macro_compute_2d.py:353-361); runs
         every 10-1000 steps, off the per-step path, so it stays a handful of torch ops."""
+        vel = resolve(vel)
         v = ((vel[..., 0:1, 2:, 1:-1] - vel[..., 0:1, :-2, 1:-1])
              - (vel[..., 1:2, 1:-1, 2:] - vel[..., 1:2, 1:-1, :-2])) / (2.0 * dx)
         return torch.nn.functional.pad(v, pad=(1, 1, 1, 1), mode="replicate")
@@ -263,6 +325,7 @@ class LBMCollision2d:
     # -- single-launch operators -------------------------------------------------------------------
     def get_feq_(self, dx, dt, rho, vel, tau=None, force=None, is_convection=False):
         """Second-order equilibrium with the half-force velocity shift (LBM_collision_2d.py:236-286)."""
+        rho, vel, force = resolve(rho), resolve(vel), resolve(force)
         B, H, W = _dims(vel, "vel")
         rho = _full(rho, (B, 1, H, W), "rho", vel)
         force = _full(force, (B, 2, H, W), "force", vel)
@@ -275,6 +338,7 @@ class LBMCollision2d:
 
     def get_grad(self, rho, dx, flags):
         """9-point isotropic gradient, collision_2d.cu:22-148 via LBM_collision_2d.py:308-309."""
+        rho, flags = resolve(rho), resolve(flags)
         B, H, W = _dims(rho, "rho")
         rho = rho.contiguous()
         out = torch.empty((B, 2, H, W), dtype=rho.dtype, device=rho.device)
@@ -285,6 +349,7 @@ class LBMCollision2d:
 
     def get_div(self, vel, dx, flags):
         """9-point isotropic divergence, collision_2d.cu:150-220 via LBM_collision_2d.py:311-312."""
+        vel, flags = resolve(vel), resolve(flags)
         B, H, W = _dims(vel, "vel")
         vel = vel.contiguous()
         out = torch.empty((B, 1, H, W), dtype=vel.dtype, device=vel.device)
@@ -298,11 +363,20 @@ class LBMCollision2d:
 
     def collision(self, dx, dt, f, rho, vel, flags, force=None, mesh_grid=None, is_convection=False, KBC_type=None,
                   **unused):
-        """f' = f + Omega(f, feq) + dt G; OBSTACLE cells keep f.  One launch of jrl_collide_f32
-        replaces LBMCollision2d.collision (LBM_collision_2d.py:473-555) including get_feq_ and the
-        axisymmetric source (:343-471) with its gradient / divergence stencils."""
-        B, H, W = _dims(f)
+        """f' = f + Omega(f, feq) + dt G; OBSTACLE cells keep f (LBMCollision2d.collision, LBM_collision_2d.py:473-555,
+        including get_feq_ and the axisymmetric source :343-471 with its gradient / divergence stencils).
+        When f, rho, vel are the still-unlaunched results of this step's propagation() [+ solve_boundary()] +
+        macro_compute(_C)(), the WHOLE step is launched here as one fused kernel (jrl_step_f32, 72 B per cell instead of
+        four passes); otherwise whatever is pending is launched call by call and this is one launch of jrl_collide_f32."""
         op, kbc, tau = self._operator(is_convection, KBC_type)
+        P = f.pending if isinstance(f, L.LazyField) else None
+        if P is not None:
+            why = self._fusable(P, dx, dt, f, rho, vel, flags, mesh_grid, is_convection, tau)
+            if why is None:
+                return self._fused_step(P, dx, dt, op, kbc, tau, force, mesh_grid, is_convection)
+            L._why(why)
+        f, rho, vel, flags, force, mesh_grid = (resolve(t) for t in (f, rho, vel, flags, force, mesh_grid))
+        B, H, W = _dims(f)
         force = _full(force, (B, 2, H, W), "force", f)
         d = N.CollideDesc()
         d.B, d.H, d.W = B, H, W
@@ -320,6 +394,78 @@ class LBMCollision2d:
         d.f_out = f_out.data_ptr()
         N.call("jrl_collide_f32", ctypes.byref(d), like=f)
         return f_out
+
+    # -- the fused step behind the four calls (jrl_lazy.py) --------------------------------------------------------
+    def _fusable(self, P, dx, dt, f, rho, vel, flags, mesh_grid, is_convection, tau):
+        """None when (f, rho, vel) are exactly this step's recorded chain and jrl_step_f32 computes it; else the reason
+        the calls are replayed one launch each."""
+        m = P.moments
+        if P.launched or m is None or not P.owns(f, P.f_role()) or flags is not P.flags:
+            return "collision() input is not this step's propagation -> macro_compute chain"
+        B, H, W = _dims(P.f_in)
+        if float(m["dx"]) != float(dx) or float(m["dt"]) != float(dt):
+            return "dx / dt differ between the calls"
+        if is_convection:
+            if m["kind"] != "C" or not P.owns(rho, "C_clamp" if P.clamp else "C"):
+                return "concentration collision without this step's macro_compute_C result"
+            if P.vel_in is None or not P.is_input(vel, P.vel_in, "vel_in") or m["vel"] is not P.vel_in:
+                return "advecting velocity differs between propagation and collision"
+            if self.axisymmetric_type != N.AXI_NOT and mesh_grid is None:
+                return "axisymmetric concentration step without mesh_grid"
+        else:
+            if m["kind"] != "fluid" or not P.owns(rho, "rho") or not P.owns(vel, "vel"):
+                return "collision without this step's macro_compute result"
+            if self.axisymmetric_type != N.AXI_NOT:
+                return "axisymmetric fluid source needs post-stream moments of the neighbours (two passes)"
+            if (P.rho_in is None or P.vel_in is None) and self._has_inflow(P.flags):
+                return "INFLOW cells with rho / vel not given to propagation()"
+            if m["obj"]._contact_angle is not None and (H < 4 or W < 4):
+                return "grid too small for the fused contact-angle ring"
+        w = P.wall
+        if w is not None:
+            if is_convection or float(w["tau"]) != float(tau) or float(w["dx"]) != float(dx) or float(w["dt"]) != float(dt):
+                return "moving-wall parameters differ from the collision's"
+            if w["vel"] is not m["vel"]:
+                return "moving wall and macro_compute were given different previous velocities"
+        if self.axisymmetric_type != P.prop.axisymmetric_type or self.axisymmetric_type != m["obj"].axisymmetric_type:
+            return "solver objects disagree on the symmetry axis"
+        return None
+
+    def _has_inflow(self, flags):
+        c = getattr(self, "_inflow_cache", None)
+        if c is None or c[0]() is not flags or c[1] != flags._version:
+            c = self._inflow_cache = (weakref.ref(flags), flags._version,
+                                      bool(((flags == 8) | (flags == CELL_INFLOW_2)).any()))
+        return c[2]
+
+    def _fused_step(self, P, dx, dt, op, kbc, tau, force, mesh_grid, is_convection):
+        import jrl_step
+        from types import SimpleNamespace
+        m = P.moments
+        ca = None if is_convection else m["obj"]._contact_angle
+        key = (op, kbc, float(tau), bool(is_convection), float(dx), float(dt), id(ca), self.axisymmetric_type)
+        cache = self.__dict__.setdefault("_fused_cache", {})
+        fs = cache.get(key)
+        if fs is None:
+            par = SimpleNamespace(tau=tau, axisymmetric_type=self.axisymmetric_type, contact_angle=ca, device=P.f_in.device)
+            name = {N.OP_BGK: "bgk", N.OP_MRT: "mrt", N.OP_KBC: "kbc"}[op]
+            fs = jrl_step.FusedStep(par, operator=name, kbc_type=kbc if op == N.OP_KBC else None, tau=tau,
+                                    tau_D=tau if is_convection else None, is_convection=is_convection, dx=dx, dt=dt,
+                                    contact_angle=ca, mrt=self._mrt if op == N.OP_MRT else None)
+            if len(cache) >= 8:
+                cache.clear()
+            cache[key] = fs
+        P.check_unmodified()
+        w = P.wall
+        out = fs.step(P.f_in, P.flags, m["rho"], m["vel"], phi_obs=P.phi_obs, force=resolve(force),
+                      mesh_grid=resolve(mesh_grid), inflow_vel=P.inflow_vel, inflow_density=P.inflow_density,
+                      use_wall=w is not None, wall_phi=None if w is None else w["phi_obs"],
+                      obs_vel=None if w is None else w["obs_vel"], clamp01=P.clamp)
+        if is_convection:
+            P.publish_fused(out[1], None)
+        else:
+            P.publish_fused(out[1], out[2])
+        return out[0]
 
 
 class LBMCollisionMRT2d(LBMCollision2d):
@@ -368,10 +514,23 @@ class LBMBoundary2d:
 
     def solve_boundary(self, dt, dx, rho, vel, flags, f, phi_obs, obs_vel, tau=None, is_convection=False):
         """Regularised moving-wall reconstruction at fluid cells next to obstacles; one launch of
-        jrl_wall_f32 (solid_fluid_coupling.cu:25-252).  `rho` and `is_convection` are unused by the
-        reference kernel too."""
-        B, H, W = _dims(f)
+        jrl_wall_f32 (solid_fluid_coupling.cu:25-252) -- recorded, not launched, when `f` is the still-unlaunched
+        result of propagation() on the same flags.  `rho` and `is_convection` are unused by the reference kernel too."""
         tau = self._tau if tau is None else tau
+        P = f.pending if isinstance(f, L.LazyField) else None
+        phi_obs, obs_vel = resolve(phi_obs), _opt(resolve(obs_vel))
+        if (P is not None and P.wall is None and P.moments is None and P.owns(f, "f_stream") and flags is P.flags
+                and (P.vel_in is None or P.is_input(vel, P.vel_in, "vel_in"))):
+            B, H, W = _dims(f)
+            vel_t = P.vel_in if P.vel_in is not None else resolve(vel)
+            N.tensor_ptr(vel_t, "vel", shape=(B, 2, H, W), like=P.f_in)
+            N.tensor_ptr(phi_obs, "phi_obs", shape=(B, 1, H, W), like=P.f_in)
+            N.tensor_ptr(obs_vel, "obs_vel", shape=(B, 2, H, W), like=P.f_in, optional=True)
+            return P.add_wall(self, dt, dx, tau, rho, vel_t, phi_obs, obs_vel)
+        return self._wall(dt, dx, tau, resolve(vel), resolve(flags), resolve(f), phi_obs, obs_vel)
+
+    def _wall(self, dt, dx, tau, vel, flags, f, phi_obs, obs_vel):
+        B, H, W = _dims(f)
         f_new = torch.empty_like(f)
         N.call("jrl_wall_f32", float(dt), float(dx), float(tau), N.tensor_ptr(vel, "vel", shape=(B, 2, H, W), like=f),
                N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f),

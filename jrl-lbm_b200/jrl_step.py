@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import weakref
 
 import torch
 
@@ -30,7 +31,7 @@ class FusedStep:
     """
 
     def __init__(self, parameters, operator="bgk", kbc_type=None, tau=None, tau_D=None, is_convection=False,
-                 dx=1.0, dt=1.0, contact_angle="from_parameters"):
+                 dx=1.0, dt=1.0, contact_angle="from_parameters", mrt=None):
         self.axisymmetric_type = int(parameters.axisymmetric_type)
         self.op = _OPS[operator]
         self.kbc_type = 0 if kbc_type is None else int(kbc_type)
@@ -45,7 +46,7 @@ class FusedStep:
                 raise RuntimeError("is_convection needs tau_D")
             self.tau = float(tau_D)
         self.dx, self.dt = float(dx), float(dt)
-        self._mrt = mrt_operator(self.tau, parameters.device) if self.op == N.OP_MRT else None
+        self._mrt = (mrt if mrt is not None else mrt_operator(self.tau, parameters.device)) if self.op == N.OP_MRT else None
         ca = parameters.contact_angle if isinstance(contact_angle, str) else contact_angle
         self.use_contact = (ca is not None) and not self.is_convection
         if self.use_contact:
@@ -56,7 +57,7 @@ class FusedStep:
         else:
             self.contact_tan = 0.0
         self.use_tile_mask = True
-        self._masks = {}  # flags.data_ptr() -> (flags._version, shape, mask tensor)
+        self._masks = {}  # id(flags) -> (weakref(flags), flags._version, mask tensor)
 
     def invalidate_masks(self):
         """Forget the cached tile masks (needed only if a flags tensor was rewritten behind torch's back,
@@ -66,18 +67,23 @@ class FusedStep:
     def _tile_mask(self, flags, B, Hs, W):
         """Packed all-FLUID summary of `flags` for the pipelined kernel (jrl_tile_mask_u8), recomputed
         only when the tensor was written since the last call (torch's version counter)."""
-        key = flags.data_ptr()
+        # The entry belongs to the tensor OBJECT (weak reference), not to its address: the caching allocator gives a
+        # freed flags buffer of one run to the next run at the same address with the same version count, and a stale
+        # all-FLUID mask would make the pipelined kernel skip flag rows that now hold obstacles (ADVICE r1).
+        key = id(flags)
         hit = self._masks.get(key)
-        if hit is not None and hit[0] == flags._version and hit[1] == tuple(flags.shape):
+        if hit is not None and hit[0]() is flags and hit[1] == flags._version:
             return hit[2]
         n = N.load().jrl_tile_mask_bytes(B, Hs, W)
         if n <= 0:
             return None
-        mask = hit[2] if hit is not None and hit[2].numel() == n else torch.empty((n,), dtype=torch.uint8, device=flags.device)
+        mask = (hit[2] if hit is not None and hit[0]() is flags and hit[2].numel() == n
+                else torch.empty((n,), dtype=torch.uint8, device=flags.device))
         N.call("jrl_tile_mask_u8", ctypes.c_void_p(flags.data_ptr()), ctypes.c_void_p(mask.data_ptr()), B, Hs, W, like=flags)
+        self._masks = {k: v for k, v in self._masks.items() if v[0]() is not None}  # drop entries of dead tensors
         if len(self._masks) >= 16:
             self._masks.clear()
-        self._masks[key] = (flags._version, tuple(flags.shape), mask)
+        self._masks[key] = (weakref.ref(flags), flags._version, mask)
         return mask
 
     def step(self, f, flags, rho=None, vel=None, *, f_out=None, rho_out=None, vel_out=None, store_moments=True,

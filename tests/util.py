@@ -20,10 +20,13 @@ STAGE_A_VEL_TOL = 5e-5
 
 
 def field_tol(case, key, tol=REL_L2_TOL):
-    """Relative-L2 bar for `key` of golden case `case` (1e-5 everywhere except the stage-A velocity)."""
-    if "jrl_fluid" in case or case.startswith("a_"):
-        if "vel" in key:
-            return STAGE_A_VEL_TOL
+    """Relative-L2 bar for `key` of golden case `case`: 1e-5 everywhere except the stage-A velocity (also where
+    stage B carries it as its advecting field C_vel) and the vorticity, a finite difference of u that amplifies
+    u's last-bit noise (the reference's CPU and CUDA runs of c2_shear_mrt differ by 1.0e-5 in `vort`, 3.4e-6 in
+    `vel`, while this library matches the CUDA run bit for bit)."""
+    stage_a = "jrl_fluid" in case or case.startswith("a_")
+    if (stage_a and "vel" in key) or (case.startswith("b_") and "C_vel" in key) or key == "vort":
+        return STAGE_A_VEL_TOL
     return tol
 
 

@@ -138,17 +138,24 @@ def role_ref(args):
     os.makedirs(OUT, exist_ok=True)
     api, dev = S.api_from_src(), torch.device("cuda:0")
     if not args.skip_goldens:
-        for name, (fn, kw) in CASES.items():
+        for name, (fn, kw) in ({} if args.no_scenarios else CASES).items():
             out = getattr(S, fn)(api, dev, **kw)
             np.savez_compressed(os.path.join(OUT, f"refcuda_{name}.npz"), **{k: v for k, v in out.items() if v is not None})
             print(f"[ref] scenario {name} done", flush=True)
         import tempfile
         work = tempfile.mkdtemp(prefix="jrl_refcuda_ref_")
+        demo_s = {}
         for name in args.demos:
             t0 = time.time()
             flat = D.run_case(name, DEMO_CASES, work, cpu=False)
+            torch.cuda.synchronize()
+            demo_s[name] = round(time.time() - t0, 2)
             np.savez_compressed(os.path.join(OUT, f"demo_refcuda_{name}.npz"), **flat)
-            print(f"[ref] demo {name}: {time.time() - t0:.1f} s", flush=True)
+            print(f"[ref] demo {name}: {demo_s[name]} s", flush=True)
+            with open(os.path.join(OUT, "demo_seconds_ref.json"), "w") as f:
+                json.dump(demo_s, f, indent=1)
+    if args.no_timing:
+        return
     rows = time_cases(S, api, dev, args.only, lambda fn, kw: [("reference (torch-CUDA, as shipped)", {})])
     with open(os.path.join(OUT, "timing_ref.json"), "w") as f:
         json.dump(rows, f, indent=1)
@@ -163,9 +170,9 @@ def role_ours(args):
     from demo_cases import DEMO_CASES
     from golden_cases import CASES
     api, dev = S.api_from_src(), torch.device("cuda:0")
-    diffs = []
+    diffs, demo_s = [], {}
     if not args.skip_goldens:
-        for name, (fn, kw) in CASES.items():
+        for name, (fn, kw) in ({} if args.no_scenarios else CASES).items():
             path = os.path.join(OUT, f"refcuda_{name}.npz")
             if not os.path.exists(path):
                 continue
@@ -188,7 +195,12 @@ def role_ours(args):
                 continue
             with np.load(path) as z:
                 ref = {k: z[k] for k in z.files}
+            t0 = time.time()
             got = D.run_case(name, DEMO_CASES, work, cpu=False)
+            torch.cuda.synchronize()
+            demo_s[name] = round(time.time() - t0, 2)
+            with open(os.path.join(OUT, "demo_seconds_ours.json"), "w") as f:
+                json.dump(demo_s, f, indent=1)
             for k, w in ref.items():
                 if w.dtype.kind in "US" or w.ndim == 0:
                     continue
@@ -204,11 +216,13 @@ def role_ours(args):
         if fn in ("shear_layer", "cylinder"):
             v.append(("this library, FusedStep.run", {"fused": "run"}))
         return v
+    with open(os.path.join(OUT, "diffs.json"), "w") as f:
+        json.dump(diffs, f, indent=1)
+    if args.no_timing:
+        return
     rows = time_cases(S, api, dev, args.only, variants)
     with open(os.path.join(OUT, "timing_ours.json"), "w") as f:
         json.dump(rows, f, indent=1)
-    with open(os.path.join(OUT, "diffs.json"), "w") as f:
-        json.dump(diffs, f, indent=1)
 
 
 def main():
@@ -217,6 +231,8 @@ def main():
     ap.add_argument("--only", nargs="*")
     ap.add_argument("--demos", nargs="*", default=DEMOS)
     ap.add_argument("--skip-goldens", action="store_true")
+    ap.add_argument("--no-scenarios", action="store_true")
+    ap.add_argument("--no-timing", action="store_true")
     args = ap.parse_args()
     if args.role == "ref":
         return role_ref(args)
@@ -230,7 +246,7 @@ def main():
                                 stderr=subprocess.STDOUT).returncode
         print(f"role {role}: exit {rc}", flush=True)
     summary = {}
-    for k in ("timing_ref", "timing_ours", "diffs"):
+    for k in ("timing_ref", "timing_ours", "diffs", "demo_seconds_ref", "demo_seconds_ours"):
         p = os.path.join(OUT, k + ".json")
         if os.path.exists(p):
             with open(p) as f:
