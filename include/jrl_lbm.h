@@ -223,9 +223,17 @@ int jrl_tile_mask_u8(const uint8_t *flags, uint8_t *mask, int B, int Hs, int W, 
  * flags and C are updated in place; phi_obs [1,1,H,W] and C_vel [1,2,H,W] are fully written.  The scalars
  * are what the demo's python holds at that step: box_cx / box_cy = the fp32 box_center tensor, walks_int =
  * int(walks + 0.5 dx), w0 = (float)(1 - t), w1 = (float)t. */
+/* Tip geometry (batch_validation.py:26-55 runs three of them): JRL_TIP_BOX = the box of
+ * demo_2d_LBM_JRL_*_cylinder.py:31-49 (phi = max(tx, ty)); demo_2d_LBM_JRL_*_InfinitePlane.py is the same box with
+ * Rg = 200, i.e. Rg_radius wider than the grid.  JRL_TIP_CONE45 = demo_2d_LBM_JRL_*_45degree.py:31-46:
+ * phi = max(ty, ((x + y) - (x1 + y1)) / sqrt(2)), (x1, y1) = box_center + box_radius in fp32 (the division by the python
+ * scalar sqrt(2) is torch-CUDA's multiplication by the fp32 reciprocal). */
+enum { JRL_TIP_BOX = 0, JRL_TIP_CONE45 = 1 };
+
 typedef struct jrl_tip_desc
 {
     int H, W;
+    int shape;              /* JRL_TIP_BOX / JRL_TIP_CONE45 */
     int is_negative;
     int walks_int, Rg_radius, radius_obs_int;
     float box_cx, box_cy, box_radius;
@@ -255,6 +263,12 @@ typedef struct jrl_walk_desc
     jrl_step_desc step;
     jrl_tip_desc tip;
     double walks, vel_obs_conv, dx, dt, box_radius, inflow_height, x_interval;
+    /* The demo's own snapshot clock (:294-303, :342): x_comp = conv_timer * vel_obs_real / radius_obs_real * radius_obs,
+     * conv_timer += dt_conv_real per step, and NO clamp of the snapshot index (the demo ends with an IndexError when it
+     * runs past the stage-A cache; here: JRL_ERR_ARG, `walks` / `conv_timer` / `steps_done` hold the state at that
+     * step).  dt_conv_real == 0 selects the algebraically equal x_comp = walks - inflow_height with a clamped index. */
+    double conv_timer, dt_conv_real, vel_obs_real, radius_obs_real, radius_obs;
+    int steps_done;
     const float *vel_snaps;
     int n_snaps;
     float *records;
@@ -264,10 +278,13 @@ int jrl_conc_walk_f32(jrl_walk_desc *w, int nsteps, void *stream);
 /* Stage A (axisymmetric tip flow, demo_2d_LBM_JRL_fluid_cylinder.py).  jrl_tip_prepare_fluid_f32: the per-step host
  * work of :205-214 in one launch -- phi_obs (CalculateObsPhi :39-49, united with the top wall), the wall velocity field
  * obs_vel = (0, vel_obs) inside the tip and 0 outside, flags = OBSTACLE and vel = (0, vel_obs) inside the tip
- * (rows < walks_int, columns < Rg_radius).  flags / vel in place; phi_obs [1,1,H,W], obs_vel [1,2,H,W] fully written. */
+ * (rows < walks_int, columns < Rg_radius).  flags / vel in place; phi_obs [1,1,H,W], obs_vel [1,2,H,W] fully written.
+ * shape = JRL_TIP_CONE45 (demo_2d_LBM_JRL_fluid_45degree.py:31-46, 201-220): "inside" is phi <= 0 instead of the box,
+ * obs_vel is zeroed on the top row, and vel = obs_vel inside. */
 typedef struct jrl_tip_fluid_desc
 {
     int H, W;
+    int shape;              /* JRL_TIP_BOX / JRL_TIP_CONE45 */
     int walks_int, Rg_radius;
     float box_cx, box_cy, box_radius, vel_obs;
     const float *mesh_grid;

@@ -1244,7 +1244,9 @@ extern "C" int jrl_conc_walk_f32(jrl_walk_desc *w, int nsteps, void *stream)
                 "step descriptor: concentration form, B = 1, C ping-pong pair, C_vel, phi_obs and mesh_grid buffers required");
     JRL_REQUIRE(d.slab_rows == 0, fn, "single-domain only");
     const long long HW = (long long)d.H * d.W;
-    double walks = w->walks;
+    double walks = w->walks, conv_timer = w->conv_timer;
+    const bool demo_clock = w->dt_conv_real != 0.0;
+    w->steps_done = 0;
     for (int i = 0; i < nsteps; ++i)
     {
         // -- host scalars, as the demo computes them (:283-284, :294-303)
@@ -1252,12 +1254,29 @@ extern "C" int jrl_conc_walk_f32(jrl_walk_desc *w, int nsteps, void *stream)
         JRL_REQUIRE(walks_int >= 1 && walks_int + 1 < d.H, fn, "the tip left the grid");
         t.walks_int = walks_int;
         t.box_cy = (float)(walks - w->box_radius);
-        const double x_comp = walks - w->inflow_height;
-        int b = (int)(x_comp / w->x_interval);
-        if (b > w->n_snaps - 1)
-            b = w->n_snaps - 1;
-        if (b < 0)
-            b = 0;
+        double x_comp;
+        int b;
+        if (demo_clock)
+        {
+            const double x_real = conv_timer * w->vel_obs_real;          // :295
+            x_comp = x_real / w->radius_obs_real * w->radius_obs;        // :296
+            b = (int)(x_comp / w->x_interval);                           // :297, not clamped: the demo raises
+            if (b < 0 || b > w->n_snaps - 1)
+            {
+                w->walks = walks;
+                w->conv_timer = conv_timer;
+                JRL_REQUIRE(false, fn, "velocity snapshot index out of range (the demo raises IndexError here)");
+            }
+        }
+        else
+        {
+            x_comp = walks - w->inflow_height;
+            b = (int)(x_comp / w->x_interval);
+            if (b > w->n_snaps - 1)
+                b = w->n_snaps - 1;
+            if (b < 0)
+                b = 0;
+        }
         t.vel0 = w->vel_snaps + (long long)b * 2 * HW;
         if (b + 1 < w->n_snaps)
         {
@@ -1300,7 +1319,10 @@ extern "C" int jrl_conc_walk_f32(jrl_walk_desc *w, int nsteps, void *stream)
         d.rho = d.rho_out;
         d.rho_out = c;
         walks += w->vel_obs_conv * w->dt;
+        conv_timer += w->dt_conv_real;                                   // :342
+        w->steps_done = i + 1;
     }
     w->walks = walks;
+    w->conv_timer = conv_timer;
     return JRL_OK;
 }

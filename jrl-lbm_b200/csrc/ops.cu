@@ -444,6 +444,21 @@ __global__ void __launch_bounds__(kThreads) k_momentum_exchange(Grid g, const fl
 //      demos -- ~15 host-driven torch ops per step (demo_2d_LBM_JRL_C_cylinder.py:283-307) -- in one launch.
 //      Arithmetic follows the torch expressions operation for operation (fp32 tensors, python scalars cast
 //      to fp32), so the fields equal the demo's bit for bit.
+// phi of the tip body before the union with the top wall: box (cylinder.py:34-36) or 45-degree cone (45degree.py:34-43)
+__device__ __forceinline__ float tip_phi(int shape, float mx, float my, float box_cx, float box_cy, float box_radius)
+{
+    const float ty = (my - box_cy) - box_radius;
+    if (shape == JRL_TIP_CONE45)
+    {
+        const float x1 = box_cx + box_radius, y1 = box_cy + box_radius;  // (box_center + box_radius)[0], [1]: fp32 tensor
+        const float cc = -(x1 + y1);
+        const float align = ((mx + my) + cc) * 0.70710678118654752440f;  // / math.sqrt(2): reciprocal multiply on CUDA
+        return ty > align ? ty : align;
+    }
+    const float tx = (mx - box_cx) - box_radius;
+    return tx > ty ? tx : ty;
+}
+
 __global__ void __launch_bounds__(kThreads) k_tip_conc(jrl_tip_desc d)
 {
     pdl_enter();
@@ -453,10 +468,8 @@ __global__ void __launch_bounds__(kThreads) k_tip_conc(jrl_tip_desc d)
         return;
     const int y = (int)(i / d.W), x = (int)(i - (long long)y * d.W);
     const float mx = d.mesh_grid[i], my = d.mesh_grid[HW + i];
-    // CalculateObsPhi_forC (:31-41): box signed distance in the max norm, united (min) with the top wall
-    const float tx = (mx - d.box_cx) - d.box_radius;
-    const float ty = (my - d.box_cy) - d.box_radius;
-    float phi = tx > ty ? tx : ty;
+    // CalculateObsPhi_forC (:31-41): signed distance of the tip body, united (min) with the top wall
+    float phi = tip_phi(d.shape, mx, my, d.box_cx, d.box_cy, d.box_radius);
     if (d.is_negative)
     {
         const float top = -(my - (float)d.H);
@@ -502,12 +515,26 @@ __global__ void __launch_bounds__(kThreads) k_tip_fluid(jrl_tip_fluid_desc d)
         return;
     const int y = (int)(i / d.W), x = (int)(i - (long long)y * d.W);
     const float mx = d.mesh_grid[i], my = d.mesh_grid[HW + i];
-    const float tx = (mx - d.box_cx) - d.box_radius;
-    const float ty = (my - d.box_cy) - d.box_radius;
-    float phi = tx > ty ? tx : ty;
+    float phi = tip_phi(d.shape, mx, my, d.box_cx, d.box_cy, d.box_radius);
     const float top = -(my - (float)d.H);
     phi = phi < top ? phi : top;
     d.phi_obs[i] = phi;
+    if (d.shape == JRL_TIP_CONE45)
+    {
+        // fluid_45degree.py:203-220: is_obs = phi <= 0; obs_vel = (0, vel_obs) there (top row zeroed); flags and vel
+        // stamped wherever is_obs (vel takes obs_vel, i.e. 0 on the top row)
+        const bool is_obs = phi <= 0.f;
+        const float wv = (is_obs && y != d.H - 1) ? d.vel_obs : 0.f;
+        d.obs_vel[i] = 0.f;
+        d.obs_vel[HW + i] = wv;
+        if (is_obs)
+        {
+            d.flags[i] = CT_OBSTACLE;
+            d.vel[i] = 0.f;
+            d.vel[HW + i] = wv;
+        }
+        return;
+    }
     const bool inside = y < d.walks_int && x < d.Rg_radius;
     d.obs_vel[i] = 0.f;
     d.obs_vel[HW + i] = inside ? d.vel_obs : 0.f;

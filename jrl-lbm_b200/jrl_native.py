@@ -23,6 +23,7 @@ LIB_PATH = os.path.join(_HERE, "libjrl_lbm.so")
 _lib = None
 
 AXI_NOT, AXI_X, AXI_Y = 0, 1, 2
+TIP_BOX, TIP_CONE45 = 0, 1
 OP_BGK, OP_MRT, OP_KBC = 0, 1, 2
 SUM_SLOTS = 64
 
@@ -47,14 +48,14 @@ class StepDesc(Structure):  # struct jrl_step_desc
 
 
 class TipDesc(Structure):  # struct jrl_tip_desc
-    _fields_ = [("H", c_int), ("W", c_int), ("is_negative", c_int), ("walks_int", c_int), ("Rg_radius", c_int),
+    _fields_ = [("H", c_int), ("W", c_int), ("shape", c_int), ("is_negative", c_int), ("walks_int", c_int), ("Rg_radius", c_int),
                 ("radius_obs_int", c_int), ("box_cx", c_float), ("box_cy", c_float), ("box_radius", c_float),
                 ("vel_obs_conv", c_float), ("w0", c_float), ("w1", c_float), ("mesh_grid", c_void_p), ("flags", c_void_p),
                 ("C", c_void_p), ("vel0", c_void_p), ("vel1", c_void_p), ("phi_obs", c_void_p), ("C_vel", c_void_p)]
 
 
 class TipFluidDesc(Structure):  # struct jrl_tip_fluid_desc
-    _fields_ = [("H", c_int), ("W", c_int), ("walks_int", c_int), ("Rg_radius", c_int), ("box_cx", c_float), ("box_cy", c_float),
+    _fields_ = [("H", c_int), ("W", c_int), ("shape", c_int), ("walks_int", c_int), ("Rg_radius", c_int), ("box_cx", c_float), ("box_cy", c_float),
                 ("box_radius", c_float), ("vel_obs", c_float), ("mesh_grid", c_void_p), ("flags", c_void_p), ("vel", c_void_p),
                 ("phi_obs", c_void_p), ("obs_vel", c_void_p)]
 
@@ -67,6 +68,8 @@ class FluidWalkDesc(Structure):  # struct jrl_fluid_walk_desc
 class WalkDesc(Structure):  # struct jrl_walk_desc
     _fields_ = [("step", StepDesc), ("tip", TipDesc), ("walks", c_double), ("vel_obs_conv", c_double), ("dx", c_double),
                 ("dt", c_double), ("box_radius", c_double), ("inflow_height", c_double), ("x_interval", c_double),
+                ("conv_timer", c_double), ("dt_conv_real", c_double), ("vel_obs_real", c_double), ("radius_obs_real", c_double),
+                ("radius_obs", c_double), ("steps_done", c_int),
                 ("vel_snaps", c_void_p), ("n_snaps", c_int), ("records", c_void_p)]
 
 

@@ -568,16 +568,17 @@ def momentum_exchange(f_post, flags):
 
 
 def tip_prepare_conc(mesh_grid, flags, C, vel0, vel1, t, box_center, box_radius, walks_int, Rg_radius, radius_obs_int,
-                     vel_obs_conv, is_negative=True, phi_out=None, vel_out=None):
+                     vel_obs_conv, is_negative=True, phi_out=None, vel_out=None, shape=N.TIP_BOX):
     """Device-side tip motion for the JRL concentration walk loop (jrl_tip_prepare_conc_f32): one launch instead
     of the demo's ~15 torch ops per step (demo_2d_LBM_JRL_C_cylinder.py:283-307).  flags and C are updated in
-    place; returns (phi_obs, C_vel).  vel0 / vel1: [2,H,W] (or [1,2,H,W]) velocity snapshots and the interpolation
+    place; returns (phi_obs, C_vel).  shape: N.TIP_BOX (cylinder, infinite plane) or N.TIP_CONE45
+    (demo_2d_LBM_JRL_C_45degree.py:31-46).  vel0 / vel1: [2,H,W] (or [1,2,H,W]) velocity snapshots and the interpolation
     weight t (vel1 None: vel0 alone); box_center: the demo's fp32 [2] tensor or a pair of floats."""
     B, H, W = _dims(C, "C")
     if B != 1:
         raise RuntimeError("tip_prepare_conc: batch size 1 only")
     d = N.TipDesc()
-    d.H, d.W, d.is_negative = H, W, int(bool(is_negative))
+    d.H, d.W, d.is_negative, d.shape = H, W, int(bool(is_negative)), int(shape)
     d.walks_int, d.Rg_radius, d.radius_obs_int = int(walks_int), int(Rg_radius), int(radius_obs_int)
     bc = box_center.detach().to("cpu", torch.float32).tolist() if isinstance(box_center, torch.Tensor) else list(box_center)
     d.box_cx, d.box_cy, d.box_radius = float(bc[0]), float(bc[1]), float(box_radius)

@@ -190,12 +190,17 @@ class FusedStep:
 
 
 def conc_walk(fs, h, flags, C, mesh_grid, vel_snaps, walks, nsteps, *, box_center_x, box_radius, Rg_radius, radius_obs_int,
-              vel_obs_conv, inflow_height, x_interval=0.1, is_negative=True, clamp01=True, dx=1.0, dt=1.0, records=None):
+              vel_obs_conv, inflow_height, x_interval=0.1, is_negative=True, clamp01=True, dx=1.0, dt=1.0, records=None,
+              shape=N.TIP_BOX, demo_clock=None):
     """`nsteps` of the JRL concentration demos' walk loop in ONE library call (jrl_conc_walk_f32): device-side
     tip motion, fused concentration step, the two recorded strip fluxes and the tip advance, per step, with no
     interpreter in the loop (demo_2d_LBM_JRL_C_cylinder.py:281-362).  `fs`: a FusedStep built with
     is_convection=True; flags and C are updated in place / ping-ponged.  Returns
-    (h, C, records [nsteps,4] = inflow flux, inflow sum, current flux, current sum, walks, phi_obs, C_vel)."""
+    (h, C, records [nsteps,4] = inflow flux, inflow sum, current flux, current sum, walks, phi_obs, C_vel).
+    shape: N.TIP_BOX / N.TIP_CONE45.  demo_clock: None, or a dict(conv_timer, dt_conv_real, vel_obs_real,
+    radius_obs_real, radius_obs) to index the velocity snapshots exactly as the demo's python does (:294-303, :342;
+    no clamp -- running past the stage-A cache raises like the demo's IndexError, after the steps that did run;
+    the dict is updated with the new conv_timer and `steps_done`)."""
     if not fs.is_convection:
         raise RuntimeError("conc_walk needs a FusedStep with is_convection=True")
     B, H, W = _dims(h)
@@ -210,7 +215,7 @@ def conc_walk(fs, h, flags, C, mesh_grid, vel_snaps, walks, nsteps, *, box_cente
     w = N.WalkDesc()
     w.step = d
     t = w.tip
-    t.H, t.W, t.is_negative = H, W, int(bool(is_negative))
+    t.H, t.W, t.is_negative, t.shape = H, W, int(bool(is_negative)), int(shape)
     t.Rg_radius, t.radius_obs_int = int(Rg_radius), int(radius_obs_int)
     t.box_cx, t.box_radius, t.vel_obs_conv = float(box_center_x), float(box_radius), float(vel_obs_conv)
     t.mesh_grid = d.mesh_grid
@@ -220,7 +225,15 @@ def conc_walk(fs, h, flags, C, mesh_grid, vel_snaps, walks, nsteps, *, box_cente
     w.vel_snaps = N.tensor_ptr(snaps, "vel_snaps", shape=(snaps.shape[0], 2, H, W), like=h)
     w.n_snaps = int(snaps.shape[0])
     w.records = N.tensor_ptr(records, "records", shape=(max(nsteps, 1), 4), like=h)
-    N.call("jrl_conc_walk_f32", ctypes.byref(w), nsteps, like=h)
+    if demo_clock is not None:
+        w.conv_timer, w.dt_conv_real = float(demo_clock["conv_timer"]), float(demo_clock["dt_conv_real"])
+        w.vel_obs_real, w.radius_obs_real = float(demo_clock["vel_obs_real"]), float(demo_clock["radius_obs_real"])
+        w.radius_obs = float(demo_clock["radius_obs"])
+    try:
+        N.call("jrl_conc_walk_f32", ctypes.byref(w), nsteps, like=h)
+    finally:
+        if demo_clock is not None:
+            demo_clock["conv_timer"], demo_clock["steps_done"] = float(w.conv_timer), int(w.steps_done)
     N.launch_count += max(0, 4 * nsteps - 1)
     try:
         torch.autograd.graph.increment_version(flags)
@@ -231,7 +244,7 @@ def conc_walk(fs, h, flags, C, mesh_grid, vel_snaps, walks, nsteps, *, box_cente
 
 
 def fluid_walk(collision, f, flags, rho, vel, mesh_grid, force, walks, nsteps, *, box_center_x, box_radius, Rg_radius, vel_obs,
-               tau, dx=1.0, dt=1.0):
+               tau, dx=1.0, dt=1.0, shape=N.TIP_BOX):
     """`nsteps` of the JRL fluid demos' loop (stage A, demo_2d_LBM_JRL_fluid_cylinder.py:203-264) in ONE library call
     (jrl_fluid_walk_f32): device-side tip motion, streaming with interpolated bounce-back, moving-wall reconstruction,
     moments, BGK collision with the axisymmetric source, tip advance.  `collision`: the LBMCollision2d object (axisymmetric
@@ -252,7 +265,7 @@ def fluid_walk(collision, f, flags, rho, vel, mesh_grid, force, walks, nsteps, *
     c.mesh_grid = N.tensor_ptr(mesh_grid, "mesh_grid", shape=(1, 2, H, W), like=f)
     phi, obs_vel = torch.empty_like(rho), torch.empty_like(vel)
     t = w.tip
-    t.H, t.W, t.Rg_radius = H, W, int(Rg_radius)
+    t.H, t.W, t.Rg_radius, t.shape = H, W, int(Rg_radius), int(shape)
     t.box_cx, t.box_radius, t.vel_obs = float(box_center_x), float(box_radius), float(vel_obs)
     t.mesh_grid = c.mesh_grid
     t.phi_obs = N.tensor_ptr(phi, "phi_obs", shape=(1, 1, H, W), like=f)

@@ -4,6 +4,17 @@ and the results must agree bit for bit."""
 import numpy as np
 
 import jrl_scenarios as S
+from util import compare_outputs
+
+
+def against_oracle(oracle, fn, kw, got, case, skip=()):
+    """The device path against the ORACLE on the same kwargs (the walk-loop rows must not only
+    agree with the product's own host-op path): the identical scenario body runs on the numpy oracle behind the
+    reference's class names (oracle/oracle_api.py), CPU tensors; integers / masks exact, floats within the bar."""
+    import torch
+    kw = {k: (v.cpu() if isinstance(v, torch.Tensor) else v) for k, v in kw.items() if k not in ("fused", "device_tip")}
+    want = getattr(S, fn)(oracle, torch.device("cpu"), **kw)
+    return compare_outputs(got, {k: v for k, v in want.items() if v is not None}, skip=skip, case=case)
 
 FUSED_CASES = {
     "shear_bgk": ("shear_layer", dict(res=(40, 32), steps=25, operator="bgk")),
@@ -26,6 +37,18 @@ def run_pair(api, device, name):
     chain = getattr(S, fn)(api, device, **kw)
     fused = getattr(S, fn)(api, device, fused=True, **kw)
     return chain, fused
+
+
+GEOMS = {"cylinder": dict(Rg=3), "plane": dict(Rg=200), "45degree": dict(Rg=3, geom="45degree", inflow_height=12.50000000000001)}
+
+
+def assert_close(a, b, exact, case=""):
+    """bit-identical, or (45-degree tip on the CPU build only: the scenario's torch-CPU `x / sqrt(2)` is a true division,
+    the kernel follows torch-CUDA's reciprocal multiply, so phi differs in the last bit) within the usual bars."""
+    if exact:
+        return assert_identical(a, b)
+    compare_outputs({k: v for k, v in b.items() if isinstance(v, np.ndarray)},
+                    {k: v for k, v in a.items() if isinstance(v, np.ndarray)}, case=case)
 
 
 def assert_identical(chain, fused):
@@ -107,12 +130,14 @@ RUN_CASES = {
 }
 
 
-def check_run_equals_steps(api, device, name):
-    """jrl_run_f32 (the time loop below the ABI) == one jrl_step_f32 per step, bit for bit."""
+def check_run_equals_steps(api, device, name, oracle=None):
+    """jrl_run_f32 (the time loop below the ABI) == one jrl_step_f32 per step, bit for bit -- and == the oracle."""
     fn, kw = RUN_CASES[name]
     stepped = getattr(S, fn)(api, device, fused=True, **kw)
     ran = getattr(S, fn)(api, device, fused="run", **kw)
     assert_identical(stepped, ran)
+    if oracle is not None:
+        against_oracle(oracle, fn, kw, ran, name)
 
 
 def check_run_sums_series(api, device):
@@ -146,35 +171,45 @@ def tip_snapshots(api, device, res, n=6, r0=2.5, inflow_height=8.50000000000001,
     return torch.cat([S.analytic_tip_velocity(mesh, inflow_height + k * x_interval, r0) for k in range(n)], dim=0).contiguous()
 
 
-def check_device_tip(api, device, is_negative=True, fused=True):
+def check_device_tip(api, device, is_negative=True, fused=True, oracle=None, geom="cylinder", exact=True):
     """Stage-B walk loop with the per-step host work done by ONE launch (jrl_tip_prepare_conc_f32) equals
     the demo's torch-op version bit for bit: fields, flags, flux series."""
-    res = (48, 32)
-    snaps = tip_snapshots(api, device, res)
-    kw = dict(res=res, balance_steps=5, walk_steps=45, radius_obs=2.50000000000001, inflow_height=8.50000000000001, Rg=3,
-              vel_obs_conv=0.03, is_negative=is_negative, clamp=is_negative, vel_snaps=snaps, x_interval=0.1, fused=fused)
+    res = (64, 32) if geom == "45degree" else (48, 32)
+    g = dict(inflow_height=8.50000000000001, **GEOMS[geom]) if "inflow_height" not in GEOMS[geom] else dict(GEOMS[geom])
+    snaps = tip_snapshots(api, device, res, inflow_height=g["inflow_height"])
+    kw = dict(res=res, balance_steps=5, walk_steps=45, radius_obs=2.50000000000001,
+              vel_obs_conv=0.03, is_negative=is_negative, clamp=is_negative and geom != "45degree", vel_snaps=snaps,
+              x_interval=0.1, fused=fused, **g)
     host = S.jrl_conc(api, device, **kw)
     dev = S.jrl_conc(api, device, device_tip=True, **kw)
-    assert_identical(host, dev)
+    assert_close(host, dev, exact)
     assert host["walks"] == dev["walks"] and np.abs(host["current"]).max() > 0
     if fused:
         # ... and the whole walk loop in one library call (jrl_conc_walk_f32): fields and flags bit for bit; the
         # flux records come from the device strip reduction (xor tree) instead of torch.sum: 1e-5
         run = S.jrl_conc(api, device, device_tip="run", **kw)
-        for k in ("C", "h", "flags", "C_balance"):
-            assert np.array_equal(run[k], host[k], equal_nan=True), k
+        assert_close({k: host[k] for k in ("C", "h", "flags", "C_balance")}, run, exact)
         assert abs(run["walks"] - host["walks"]) < 1e-9
         for k in ("inflow", "current"):
             a, b = np.asarray(run[k], np.float64), np.asarray(host[k], np.float64)
             assert np.linalg.norm(a - b) <= 1e-5 * np.linalg.norm(b), k
+    if oracle is not None:
+        # the demo's `vel_snaps` interpolation branch (demo_2d_LBM_JRL_C_cylinder.py:294-303) on the oracle, against
+        # the device-side tip motion and against the whole walk loop below the ABI
+        against_oracle(oracle, "jrl_conc", kw, dev, "jrl_conc_device_tip")
+        if fused:
+            against_oracle(oracle, "jrl_conc", kw, run, "jrl_conc_walk")
 
 
-def check_fluid_walk(api, device, gravity=2e-5):
+def check_fluid_walk(api, device, gravity=2e-5, oracle=None, geom="cylinder", exact=True):
     """Stage-A loop in one library call (jrl_fluid_walk_f32) equals the demo's loop (solver objects + host torch ops
     for the tip) bit for bit."""
-    kw = dict(res=(48, 32), steps=70, radius_obs=2.50000000000001, inflow_height=8.50000000000001, Rg=3, vel_obs=0.02,
-              gravity_strength=gravity, snapshots=(25,))
+    g = dict(inflow_height=8.50000000000001, **GEOMS[geom]) if "inflow_height" not in GEOMS[geom] else dict(GEOMS[geom])
+    kw = dict(res=(64, 32) if geom == "45degree" else (48, 32), steps=70, radius_obs=2.50000000000001, vel_obs=0.02,
+              gravity_strength=gravity, snapshots=(25,), **g)
     host = S.jrl_fluid(api, device, **kw)
     run = S.jrl_fluid(api, device, device_tip="run", **kw)
-    assert_identical(host, run)
+    assert_close(host, run, exact, case="a_" + geom)
     assert abs(host["walks"] - run["walks"]) < 1e-12
+    if oracle is not None:
+        against_oracle(oracle, "jrl_fluid", kw, run, "jrl_fluid_walk")

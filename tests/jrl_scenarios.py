@@ -197,10 +197,21 @@ def cylinder(api, device, res=(800, 400), D=20, steps=2000, Re=5000.0, Vmax=0.05
 #   (demo/demo_2d_LBM_JRL_fluid_cylinder.py:39-268)
 # ------------------------------------------------------------------------------------------------
 
-def tip_phi(api, mesh_grid, box_center, box_radius, is_negative=True):
+def tip_phi(api, mesh_grid, box_center, box_radius, is_negative=True, geom="cylinder"):
     """CalculateObsPhi / CalculateObsPhi_forC: box signed distance (max norm) united with the
-    top wall, demo_2d_LBM_JRL_fluid_cylinder.py:39-49, demo_2d_LBM_JRL_C_cylinder.py:31-41."""
+    top wall, demo_2d_LBM_JRL_fluid_cylinder.py:39-49, demo_2d_LBM_JRL_C_cylinder.py:31-41 (the infinite-plane demos
+    use the same function with Rg = 200); geom="45degree": the cone of demo_2d_LBM_JRL_*_45degree.py:31-46."""
     res_y = mesh_grid.shape[-2]
+    if geom == "45degree":
+        x, y = mesh_grid[:, 0:1], mesh_grid[:, 1:2]
+        phi = (y - box_center[1]) - box_radius
+        x1 = (box_center + box_radius)[0]
+        y1 = (box_center + box_radius)[1]
+        A_, B_, C_ = 1.0, 1.0, -(x1 + y1)
+        phi = torch.maximum(phi, (A_ * x + B_ * y + C_) / math.sqrt(2))
+        if is_negative:
+            phi = api.UnionPhiObs(phi, -(y - res_y), alpha=1)
+        return phi
     tx = (mesh_grid[:, 0:1] - box_center[0]) - box_radius
     ty = (mesh_grid[:, 1:2] - box_center[1]) - box_radius
     phi = torch.maximum(tx, ty)
@@ -211,7 +222,7 @@ def tip_phi(api, mesh_grid, box_center, box_radius, is_negative=True):
 
 def jrl_fluid(api, device, res=(128, 64), steps=200, Re=3e-4, gravity_strength=0.0, radius_obs=6.50000000000001,
               inflow_height=20.50000000000001, Rg=4, vel_obs=None, x_interval=0.1, dx=1, dt=1, tau=1.0,
-              snapshots=(), device_tip=False):
+              snapshots=(), device_tip=False, geom="cylinder"):
     """Stage A with the demo's per-step host work (phi / flags / wall velocity restamp) kept as
     torch ops.  `vel_obs` defaults to Re*visc/radius_obs as in the demo (:78); tests pass a
     larger value so the tip crosses cells within a few hundred steps.  `gravity_strength` is
@@ -252,9 +263,10 @@ def jrl_fluid(api, device, res=(128, 64), steps=200, Re=3e-4, gravity_strength=0
     walks = inflow_height
     walks_int = inflow_height_int
     box_center = torch.Tensor([Rg_radius - box_radius, walks - box_radius]).to(device).to(dtype)
-    flags[..., 0:walks_int, 0:Rg_radius] = int(CT.OBSTACLE)
-    vel[..., 0, 0:walks_int, 0:Rg_radius] = 0
-    vel[..., 1, 0:walks_int, 0:Rg_radius] = vel_obs
+    if geom != "45degree":  # demo_2d_LBM_JRL_fluid_cylinder.py:193-195; the 45-degree demo stamps in the loop only
+        flags[..., 0:walks_int, 0:Rg_radius] = int(CT.OBSTACLE)
+        vel[..., 0, 0:walks_int, 0:Rg_radius] = 0
+        vel[..., 1, 0:walks_int, 0:Rg_radius] = vel_obs
     out = {}
     if device_tip == "run":  # extension of this repo: the whole loop below the C ABI (jrl_fluid_walk_f32)
         import jrl_step
@@ -262,7 +274,8 @@ def jrl_fluid(api, device, res=(128, 64), steps=200, Re=3e-4, gravity_strength=0
         for stop in sorted(set(int(x) for x in snapshots if 0 < int(x) < steps)) + [steps]:
             f, density, vel, walks, phi_obs, phi_obs_vel = jrl_step.fluid_walk(
                 collision_f, f, flags, density, vel, mesh_grid, force, walks, stop - done, box_center_x=float(box_center[0]),
-                box_radius=box_radius, Rg_radius=Rg_radius, vel_obs=vel_obs, tau=tau, dx=dx, dt=dt)
+                box_radius=box_radius, Rg_radius=Rg_radius, vel_obs=vel_obs, tau=tau, dx=dx, dt=dt,
+                shape=1 if geom == "45degree" else 0)
             done = stop
             if done in snapshots:
                 out[f"snap_{done}_rho"] = _np(density)
@@ -271,12 +284,21 @@ def jrl_fluid(api, device, res=(128, 64), steps=200, Re=3e-4, gravity_strength=0
     for step in range(steps):
         walks_int = int(walks + 0.5 * dx)
         box_center[1] = walks - box_radius
-        phi_obs = tip_phi(api, mesh_grid, box_center, box_radius)
-        phi_obs_vel = torch.zeros_like(vel)
-        phi_obs_vel[..., 1, 0:walks_int, 0:Rg_radius] = vel_obs
-        flags[..., 0:walks_int, 0:Rg_radius] = int(CT.OBSTACLE)
-        vel[..., 0, 0:walks_int, 0:Rg_radius] = 0
-        vel[..., 1, 0:walks_int, 0:Rg_radius] = vel_obs
+        phi_obs = tip_phi(api, mesh_grid, box_center, box_radius, geom=geom)
+        if geom == "45degree":                                            # demo_2d_LBM_JRL_fluid_45degree.py:203-220
+            is_obs = phi_obs <= 0
+            phi_obs_vel = torch.where(is_obs.repeat(1, 2, 1, 1),
+                                      torch.Tensor([0, vel_obs]).to(device).to(dtype).reshape(1, 2, 1, 1).expand_as(vel),
+                                      torch.zeros_like(vel))
+            phi_obs_vel[:, :, -1, :] = 0
+            flags[is_obs] = int(CT.OBSTACLE)
+            vel = torch.where(is_obs.repeat(1, 2, 1, 1), phi_obs_vel, vel)
+        else:
+            phi_obs_vel = torch.zeros_like(vel)
+            phi_obs_vel[..., 1, 0:walks_int, 0:Rg_radius] = vel_obs
+            flags[..., 0:walks_int, 0:Rg_radius] = int(CT.OBSTACLE)
+            vel[..., 0, 0:walks_int, 0:Rg_radius] = 0
+            vel[..., 1, 0:walks_int, 0:Rg_radius] = vel_obs
         f = prop.propagation(f=f, flags=flags, phi_obs=phi_obs, rho=density, vel=vel)
         f = coupling.solve_boundary(dt=dt, dx=dx, rho=density, vel=vel, flags=flags, f=f, phi_obs=phi_obs,
                                     obs_vel=phi_obs_vel, tau=tau)
@@ -309,7 +331,7 @@ def analytic_tip_velocity(mesh_grid, walks, r0):
 
 def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0.34013, radius_obs=6.50000000000001,
              inflow_height=20.50000000000001, Rg=4, vel_obs_conv=None, is_negative=True, clamp=True,
-             dx=1, dt=1, vel_field=None, fused=False, vel_snaps=None, x_interval=0.1, device_tip=False):
+             dx=1, dt=1, vel_field=None, fused=False, vel_snaps=None, x_interval=0.1, device_tip=False, geom="cylinder"):
     """Stage B.  `vel_field`: callable(mesh_grid, walks) -> normalised [1,2,H,W] velocity
     (defaults to `analytic_tip_velocity`); the demo interpolates HDF5 snapshots instead
     (:294-303).  `vel_snaps` [n,2,H,W]: velocity snapshots at tip travel 0, x_interval, 2 x_interval, ...
@@ -347,7 +369,7 @@ def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0
     C_flags[..., 1:-1, 1:-1] = int(CT.FLUID)
     C_flags[..., 0] = int(CT.FLUID)
     C_flags[..., -1, :] = int(CT.OBSTACLE) if is_negative else int(CT.INFLOW_2)
-    C_flags[..., :-1, -1] = int(CT.INFLOW_2)
+    C_flags[..., :-1, -1] = int(CT.INFLOW_2) if (is_negative or geom != "45degree") else int(CT.OUTFLOW)
     C_flags[..., 0, Rg_radius:] = int(CT.INFLOW_2)
     C_flags[..., 0:inflow_height_int, 0:Rg_radius] = int(CT.OBSTACLE)
     C_flags[..., inflow_height_int - 1, 0:radius_obs_int] = int(CT.INFLOW)
@@ -358,7 +380,10 @@ def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0
     walks = inflow_height
     walks_int = inflow_height_int
     box_center = torch.Tensor([Rg_radius - box_radius, walks - box_radius]).to(device).to(dtype)
-    C_flags[..., 0:walks_int, 0:Rg_radius] = int(CT.OBSTACLE)
+    if geom == "45degree":                                                # demo_2d_LBM_JRL_C_45degree.py:211-216
+        C_flags[tip_phi(api, mesh_grid, box_center, box_radius, is_negative, geom) <= 0] = int(CT.OBSTACLE)
+    else:
+        C_flags[..., 0:walks_int, 0:Rg_radius] = int(CT.OBSTACLE)
     C_flags[..., walks_int - 1, 0:radius_obs_int] = int(CT.INFLOW)
     C[C_flags == int(CT.OBSTACLE)] = 0.0
     balance = []
@@ -383,8 +408,10 @@ def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0
         h, C, rec, walks, phi_obs, C_vel = jrl_step.conc_walk(
             fs, h, C_flags, C, mesh_grid, vel_snaps, walks, walk_steps, box_center_x=float(box_center[0]), box_radius=box_radius,
             Rg_radius=Rg_radius, radius_obs_int=radius_obs_int, vel_obs_conv=vel_obs_conv, inflow_height=inflow_height,
-            x_interval=x_interval, is_negative=is_negative, clamp01=clamp, dx=dx, dt=dt)
-        inflow, current = list(rec[:, 0]), list(rec[:, 2])
+            x_interval=x_interval, is_negative=is_negative, clamp01=clamp, dx=dx, dt=dt,
+            shape=1 if geom == "45degree" else 0)
+        col = 1 if geom == "45degree" else 0   # the 45-degree demo records the plain strip sums (:353-376)
+        inflow, current = list(rec[:, col]), list(rec[:, 2 + col])
         for _ in range(walk_steps):
             R.step()
         walk_steps = 0
@@ -402,9 +429,9 @@ def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0
             phi_obs, C_vel = jrl_solver.tip_prepare_conc(
                 mesh_grid, C_flags, C, vel_snaps[batch_idx], None if t_w is None else vel_snaps[batch_idx + 1],
                 0.0 if t_w is None else t_w, box_center, box_radius, walks_int, Rg_radius, radius_obs_int, vel_obs_conv,
-                is_negative=is_negative, phi_out=phi_buf, vel_out=vel_buf)
+                is_negative=is_negative, phi_out=phi_buf, vel_out=vel_buf, shape=1 if geom == "45degree" else 0)
         else:
-            phi_obs = tip_phi(api, mesh_grid, box_center, box_radius, is_negative)
+            phi_obs = tip_phi(api, mesh_grid, box_center, box_radius, is_negative, geom)
             if not is_negative:
                 C_flags[..., -1, :] = int(CT.INFLOW_2)
             C_flags[phi_obs < 0] = int(CT.OBSTACLE)
@@ -432,6 +459,9 @@ def jrl_conc(api, device, res=(128, 64), balance_steps=200, walk_steps=200, Pe=0
             h = collision_h.collision(dx=dx, dt=dt, f=h, rho=C, vel=C_vel, flags=C_flags, force=None,
                                       mesh_grid=mesh_grid, is_convection=True, KBC_type=int(api.KBCType.KBC_C))
         for y0, series in ((walks_int, inflow), (walks_int + 1, current)):
+            if geom == "45degree":                                        # demo_2d_LBM_JRL_C_45degree.py:353-376
+                series.append(((C)[..., y0, 0:radius_obs_int].flatten() * area).sum())
+                continue
             dC_z = ((C)[..., y0, 0:radius_obs_int] - (C)[..., y0 - 1, 0:radius_obs_int]).flatten()
             r = mesh_grid[..., 0:1, y0, 0:radius_obs_int + 1].flatten()
             rC = r * (C)[..., y0, 0:radius_obs_int + 1].flatten()

@@ -21,8 +21,8 @@ def test_tile_mask(emu_api):
 
 
 @pytest.mark.parametrize("name", list(RUN_CASES))
-def test_run_equals_steps(emu_api, name):
-    check_run_equals_steps(emu_api, torch.device("cpu"), name)
+def test_run_equals_steps(emu_api, oracle_api, name):
+    check_run_equals_steps(emu_api, torch.device("cpu"), name, oracle=oracle_api)
 
 
 def test_run_sums_series(emu_api):
@@ -30,10 +30,21 @@ def test_run_sums_series(emu_api):
 
 
 @pytest.mark.parametrize("is_negative,fused", [(True, True), (False, True), (True, False)])
-def test_device_tip_motion(emu_api, is_negative, fused):
-    check_device_tip(emu_api, torch.device("cpu"), is_negative=is_negative, fused=fused)
+def test_device_tip_motion(emu_api, oracle_api, is_negative, fused):
+    check_device_tip(emu_api, torch.device("cpu"), is_negative=is_negative, fused=fused, oracle=oracle_api)
 
 
 @pytest.mark.parametrize("gravity", [2e-5, 0.0])
-def test_fluid_walk(emu_api, gravity):
-    check_fluid_walk(emu_api, torch.device("cpu"), gravity)
+def test_fluid_walk(emu_api, oracle_api, gravity):
+    check_fluid_walk(emu_api, torch.device("cpu"), gravity, oracle=oracle_api)
+
+
+@pytest.mark.parametrize("geom", ["plane", "45degree"])
+def test_device_tip_motion_geometries(emu_api, oracle_api, geom):
+    """batch_validation.py's other tips (infinite plane, 45-degree cone) on the device-side tip motion and the walk loop."""
+    check_device_tip(emu_api, torch.device("cpu"), is_negative=True, fused=True, oracle=oracle_api, geom=geom, exact=geom != "45degree")
+
+
+@pytest.mark.parametrize("geom", ["plane", "45degree"])
+def test_fluid_walk_geometries(emu_api, oracle_api, geom):
+    check_fluid_walk(emu_api, torch.device("cpu"), 2e-5, oracle=oracle_api, geom=geom, exact=geom != "45degree")

@@ -114,18 +114,18 @@ def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym
 
 
 @pytest.mark.parametrize("name", list(RUN_CASES))
-def test_run_equals_steps(cuda_api, dev, name):
-    check_run_equals_steps(cuda_api, dev, name)
+def test_run_equals_steps(cuda_api, oracle_api, dev, name):
+    check_run_equals_steps(cuda_api, dev, name, oracle=oracle_api)
 
 
 @pytest.mark.parametrize("is_negative,fused", [(True, True), (False, True), (True, False)])
-def test_device_tip_motion(cuda_api, dev, is_negative, fused):
-    check_device_tip(cuda_api, dev, is_negative=is_negative, fused=fused)
+def test_device_tip_motion(cuda_api, oracle_api, dev, is_negative, fused):
+    check_device_tip(cuda_api, dev, is_negative=is_negative, fused=fused, oracle=oracle_api)
 
 
 @pytest.mark.parametrize("gravity", [2e-5, 0.0])
-def test_fluid_walk(cuda_api, dev, gravity):
-    check_fluid_walk(cuda_api, dev, gravity)
+def test_fluid_walk(cuda_api, oracle_api, dev, gravity):
+    check_fluid_walk(cuda_api, dev, gravity, oracle=oracle_api)
 
 
 def test_run_sums_series(cuda_api, dev):
@@ -201,3 +201,14 @@ def test_error_behaviour(cuda_api, dev):
     with pytest.raises(RuntimeError, match="KBC Type"):
         R.create_collision_KBC().collision(dx=1, dt=1, f=f, rho=f[:, :1].contiguous(), vel=f[:, :2].contiguous(),
                                            flags=flags, force=None, KBC_type=7)
+
+
+@pytest.mark.parametrize("geom", ["plane", "45degree"])
+def test_device_tip_motion_geometries(cuda_api, oracle_api, dev, geom):
+    """batch_validation.py's other tips (infinite plane, 45-degree cone) on the device-side tip motion and the walk loop."""
+    check_device_tip(cuda_api, dev, is_negative=True, fused=True, oracle=oracle_api, geom=geom, exact=True)
+
+
+@pytest.mark.parametrize("geom", ["plane", "45degree"])
+def test_fluid_walk_geometries(cuda_api, oracle_api, dev, geom):
+    check_fluid_walk(cuda_api, dev, 2e-5, oracle=oracle_api, geom=geom, exact=True)
