@@ -36,6 +36,7 @@ METRIC = "D2Q9 MLUPS (fused stream+collide, fp32) with achieved HBM GB/s vs roof
 UNIT = "MLUPS"
 BYTES_PER_LUP = 72.0     # 9 fp32 reads + 9 fp32 writes; flags / rho / u traffic not counted
 OUT_EVERY = 10           # demo_2d_LBM.py:121
+PRE_ROLL_S = 0.6          # untimed steps under load (and under the clock sampler) before the timed region
 FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md, used only if MEASURED_PEAKS.json is absent
 
 
@@ -49,6 +50,8 @@ def parse_args():
                     help="H = W of the periodic shear-layer grid (default: the BASELINE 32768)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end (host-buffer) leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the extra BASELINE configs (c2 / c3 / c4 at 8192^2)")
+    ap.add_argument("--e2e-full-flags", action="store_true", help="e2e leg uploads the whole flags field every step (round-1 behaviour)")
     return ap.parse_args()
 
 
@@ -65,51 +68,86 @@ def measured_peak():
 # clocks during the timed region (B200_PROFILING.md recipe)
 # ---------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons sampled every ~5 ms through NVML (nvidia_ml_py) on a thread, so that even the
+    30 ms timed region of the 8-GPU run holds samples; falls back to `nvidia-smi -lms` when NVML is not importable.
+    `mark()` brackets the timed region: only samples between the marks are summarised (the region is preceded by at
+    least PRE_ROLL_S of untimed steps under the same sampler, so the clocks are the ones under load)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index = index
-        self.rows = []
-        self.proc = None
+        self.index, self.rows, self.proc, self.marks, self.stop = index, [], None, [], False
+        self.nvml = None
 
     def __enter__(self):
         try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.index]) if vis and vis.split(",")[self.index].isdigit() else self.index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return self
+        except Exception:
+            self.nvml = None
+        try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "20", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
             self.proc = None
         return self
 
+    def _poll(self):
+        n = self.nvml
+        bits = {"hw_slowdown": n.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": n.nvmlClocksThrottleReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": n.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": n.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop:
+            try:
+                sm = float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
+                r = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.rows.append((time.perf_counter(), sm, self.smax, [k for k, b in bits.items() if r & b]))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
     def _read(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            c = [x.strip() for x in line.split(",")]
+            try:
+                self.rows.append((time.perf_counter(), float(c[1]), float(c[2]),
+                                  [n for n, v in zip(names, c[5:9]) if v.lower().startswith("active")]))
+            except Exception:
+                pass
+
+    def mark(self):
+        self.marks.append(time.perf_counter())
 
     def __exit__(self, *a):
+        self.stop = True
         if self.proc is not None:
-            time.sleep(0.15)
+            time.sleep(0.05)
             self.proc.terminate()
+        if getattr(self, "t", None) is not None:
             self.t.join(timeout=2)
 
     def summary(self):
-        sm, smax, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[1]))
-                smax.append(float(r[2]))
-                for n, v in zip(names, r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
-            except Exception:
-                pass
-        if not sm:
+        rows = self.rows
+        inside = [r for r in rows if len(self.marks) >= 2 and self.marks[0] <= r[0] <= self.marks[-1]]
+        use = inside if inside else rows
+        if not use:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(smax), "reasons": sorted(reasons), "samples": len(sm)}
+        sm = sorted(r[1] for r in use)
+        reasons = sorted({x for r in use for x in r[3]})
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(r[2] for r in use), "reasons": reasons,
+                "samples": len(inside), "samples_under_load_window": len(rows),
+                "source": "nvml, 5 ms period" if self.nvml is not None else "nvidia-smi -lms 20"}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -198,12 +236,19 @@ def cpu_reference_run(G_full, steps, warmup, sample_grid=None, budget_s=20.0):
     tau = shear_tau(G_full)
     import ref_cpu
     kind = "reference" if ref_cpu.have_ref_lib() else "port"
+    # all host cores this process may use, at every N: torch.distributed.run exports OMP_NUM_THREADS=1, which made the
+    # round-1 CPU arm 7x slower under torchrun than alone
+    try:
+        threads = len(os.sched_getaffinity(0))
+    except AttributeError:
+        threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
     Gs = sample_grid or (2048 if kind == "reference" else 512)
     rho, vel = shear_rows(Gs, torch.arange(Gs), cpu)
     flags = torch.ones((1, 1, Gs, Gs), dtype=torch.uint8)
     if kind == "reference":
         import ref_torch_port as RP
-        loop = RP.ReferenceCpuLoop(tau)
+        loop = RP.ReferenceCpuLoop(tau, threads=threads)
         cores = loop.cores
         f = RP.get_feq(1.0, 1.0, rho, vel)
         state = [f, rho, vel]
@@ -239,49 +284,186 @@ def cpu_reference_run(G_full, steps, warmup, sample_grid=None, budget_s=20.0):
     return mlups, info, dt / done * 1e3, done
 
 
-def run_e2e(wl, K, Wm, device, barrier):
-    """The same steps through the public API (FusedStep / SlabLattice) with HOST buffers in the loop:
-    every step uploads that step's flags field (uint8 [rows, G], authored on the host, pinned memory; a
-    host-driven moving obstacle rewrites it every step as the JRL demos do, demo_2d_LBM_JRL_fluid_
-    cylinder.py:212) and downloads the step's result, the mass / momentum sums reduced inside the step
-    kernel (jrl_step_desc.sums).  Uploads run one step ahead on a copy stream into a double buffer; the
-    downloads are asynchronous into a pinned ring and all have landed when the timed region closes.
+E2E_BAND_ROWS = 64
+
+
+def run_e2e(wl, K, Wm, device, barrier, full_flags=False):
+    """The same steps through the public API (FusedStep / SlabLattice) with HOST buffers in the loop.  The host owns
+    the flags field and a host-driven moving obstacle rewrites part of it every step (as the JRL demos do,
+    demo_2d_LBM_JRL_fluid_cylinder.py:205-214): per step the DIRTY ROWS -- a band of E2E_BAND_ROWS rows that moves one
+    row per step -- are uploaded from pinned host memory into the device flags field (full_flags=True: the whole uint8
+    field, the round-1 behaviour, PCIe-bound at 1 B per cell), the packed tile mask is rebuilt because flags changed,
+    the step runs, and its result -- the mass / momentum sums reduced inside the step kernel (jrl_step_desc.sums) -- is
+    downloaded into a pinned ring; all downloads have landed when the timed region closes.
     Returns (seconds for K steps on this rank, h2d bytes/step, d2h bytes/step, host_sums[K,4])."""
     import jrl_native
     S = jrl_native.SUM_SLOTS
     total = K + Wm
-    flags_host = torch.ones(wl.flags.shape, dtype=torch.uint8).pin_memory()
-    bufs = [torch.empty_like(wl.flags), torch.empty_like(wl.flags)]
+    rows_dev = wl.flags.shape[2]
+    R = rows_dev if full_flags else min(E2E_BAND_ROWS, max(1, rows_dev - 2))
+    band_host = torch.ones((1, 1, R, wl.flags.shape[3]), dtype=torch.uint8).pin_memory()
     copy_stream = torch.cuda.Stream(device)
     main = torch.cuda.current_stream(device)
-    ready = [torch.cuda.Event(), torch.cuda.Event()]
-    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+    ready, consumed = torch.cuda.Event(), torch.cuda.Event()
     sums = torch.zeros((total, S, 4), dtype=torch.float64, device=device)
     host_sums = torch.empty((total, S, 4), dtype=torch.float64).pin_memory()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    span = max(1, rows_dev - R - 1)
 
     def upload(i):
+        y0 = 0 if full_flags else 1 + (i % span)
         with torch.cuda.stream(copy_stream):
-            if i >= 2:
-                copy_stream.wait_event(consumed[i % 2])
-            bufs[i % 2].copy_(flags_host, non_blocking=True)
-            ready[i % 2].record(copy_stream)
+            if i > 0:
+                copy_stream.wait_event(consumed)     # the previous step has read the flags this copy overwrites
+            wl.flags[:, :, y0:y0 + R].copy_(band_host, non_blocking=True)
+            ready.record(copy_stream)
 
-    upload(0)
     for i in range(total):
         if i == Wm:
             barrier()
             e0.record()
-            upload(i)                    # the timed region holds all K uploads
-        if i + 1 < total and i + 1 != Wm:
-            upload(i + 1)
-        main.wait_event(ready[i % 2])
-        wl.step(flags=bufs[i % 2], sums=sums[i])
-        consumed[i % 2].record(main)
+        upload(i)
+        main.wait_event(ready)
+        wl.step(flags=wl.flags, sums=sums[i])
+        consumed.record(main)
         host_sums[i].copy_(sums[i], non_blocking=True)
     e1.record()
     barrier()
-    return e0.elapsed_time(e1) * 1e-3, flags_host.numel(), S * 4 * 8, host_sums[Wm:].sum(dim=1)
+    return e0.elapsed_time(e1) * 1e-3, band_host.numel(), S * 4 * 8, host_sums[Wm:].sum(dim=1)
+
+
+def _event_ms(step, K, warm, barrier, world, device):
+    import torch.distributed as dist
+    for _ in range(warm):
+        step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1) / K], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def extra_configs(device, rank, world, barrier, peak, G2=8192, K=20):
+    """The other BASELINE configs at their bandwidth-bound size, measured in the same process
+    after the headline: 20 CUDA-event-timed steps each after 3 warm-up steps, inputs (>= 4.8 GB) far larger than L2.
+    At N > 1 only c4_conc_scaled (the config BASELINE shards over row slabs) runs.  `frac` = algorithmic bytes per
+    step / time / measured HBM peak, with the per-cell byte count stated per entry."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import jrl_slab
+    import jrl_step
+    import workloads as WL
+    from src.LBM.simulation import SimulationParameters, SimulationRunner
+    out = {}
+
+    def entry(ms, cells_per_gpu, bytes_per_cell, what, **kw):
+        gbs = bytes_per_cell * cells_per_gpu / (ms * 1e-3) / 1e9
+        return dict(ms_per_step=ms, mlups=cells_per_gpu * world / ms / 1e3, bytes_per_cell=bytes_per_cell,
+                    algorithmic_bytes_per_step=bytes_per_cell * cells_per_gpu, achieved_gbs=gbs, frac=gbs / peak, what=what, **kw)
+
+    if world == 1:
+        G = G2
+        rho, vel = shear_rows(G, torch.arange(G), device)
+        flags = torch.ones((1, 1, G, G), dtype=torch.uint8, device=device)
+        for name, op, kt in (("c2_mrt", "mrt", None), ("c2_kbc_a", "kbc", 133)):
+            P = SimulationParameters(simulation_size=(1, 1, G, G), device=device, contact_angle=None, tau=shear_tau(G))
+            R = SimulationRunner(P)
+            fs = R.create_fused_step(operator=op, kbc_type=kt)
+            st = [R.create_collision().get_feq_(dx=1.0, dt=1.0, rho=rho, vel=vel), None]
+            st[1] = torch.empty_like(st[0])
+
+            def step():
+                fs.step(st[0], flags, None, None, f_out=st[1], store_moments=False)
+                st[0], st[1] = st[1], st[0]
+            out[name] = entry(_event_ms(step, K, 3, barrier, world, device), G * G, 72.0,
+                              f"demo_2d_LBM_KBC.py shear layer at {G}^2, {op.upper()}{'' if kt is None else ' type %d' % kt}, fused step, moments not stored")
+            del st
+        # the reference's API, unchanged demo loop body (demo_2d_LBM.py:101-119): three solver-object calls per step,
+        # which jrl_lazy turns into one fused launch; next to the explicit FusedStep call on the same buffers
+        P = SimulationParameters(dim=2, dtype=torch.float32, device=device, simulation_size=(1, 1, G, G), dt=1.0,
+                                 contact_angle=None, Q=9, tau=shear_tau(G))
+        R = SimulationRunner(P)
+        prop, macro, col = R.create_propagation(), R.create_macro_compute(), R.create_collision()
+        st = dict(f=col.get_feq_(dx=1.0, dt=1.0, rho=rho, vel=vel), rho=rho.clone(), vel=vel.clone())
+        force = torch.zeros((1, 2, G, G), dtype=torch.float32, device=device)
+
+        def demo_step():
+            f = prop.propagation(f=st["f"], flags=flags)
+            st["rho"], st["vel"] = macro.macro_compute(dx=1.0, dt=1.0, f=f, rho=st["rho"], vel=st["vel"], flags=flags)
+            st["f"] = col.collision(dx=1.0, dt=1.0, f=f, rho=st["rho"], vel=st["vel"], flags=flags, force=force, KBC_type=None)
+        import jrl_native
+        n0 = jrl_native.launch_count
+        ms_api = _event_ms(demo_step, K, 3, barrier, world, device)
+        per_step = (jrl_native.launch_count - n0) / (K + 3)
+        fs = R.create_fused_step(operator="bgk")
+        bufs = [st["f"], torch.empty_like(st["f"]), st["rho"], torch.empty_like(st["rho"]), st["vel"], torch.empty_like(st["vel"])]
+
+        def fused_step():
+            fs.step(bufs[0], flags, bufs[2], bufs[4], f_out=bufs[1], rho_out=bufs[3], vel_out=bufs[5], force=force)
+            bufs[0], bufs[1], bufs[2], bufs[3], bufs[4], bufs[5] = bufs[1], bufs[0], bufs[3], bufs[2], bufs[5], bufs[4]
+        ms_fs = _event_ms(fused_step, K, 3, barrier, world, device)
+        out["c1_reference_api"] = entry(ms_api, G * G, 84.0, f"demo_2d_LBM.py loop body UNCHANGED (prop.propagation -> macro.macro_compute -> "
+                                        f"collision.collision) at {G}^2: {per_step:.2f} library launches per step; 72 B populations + 12 B "
+                                        "rho, u stored every step as that API returns them", launches_per_step=per_step,
+                                        fused_step_same_buffers_ms=ms_fs, ratio_to_fused_step=ms_api / ms_fs)
+        del st, bufs, force
+        torch.cuda.empty_cache()
+        # C3 scaled: flow past a cylinder, MRT + moving-wall step + inflow / outflow + contact-angle ring
+        H, W, D = G, G, 205
+        cflags, phi, crho, cvel, inflow_vel = WL.cylinder_state(device, H, W, D, (2048.0, 2048.0))
+        tau = WL.cylinder_tau(H, W)
+        P = SimulationParameters(dim=2, dtype=torch.float32, device=device, simulation_size=(1, 1, H, W), dt=1.0, density_gas=0,
+                                 density_fluid=1.0, contact_angle=torch.Tensor([0.5 * math.pi]).to(device), Q=9, tau=tau)
+        R = SimulationRunner(P)
+        col = R.create_collision_MRT()
+        col.preset_KBC(dx=1.0, dt=1.0, tau=tau)
+        fs = R.create_fused_step(operator="mrt")
+        f0 = col.get_feq_(dx=1.0, dt=1.0, rho=crho, vel=cvel)
+        b = [f0, torch.empty_like(f0), crho, torch.empty_like(crho), cvel, torch.empty_like(cvel)]
+        zero = torch.zeros_like(cvel)
+
+        def cyl_step():
+            fs.step(b[0], cflags, b[2], b[4], f_out=b[1], rho_out=b[3], vel_out=b[5], inflow_density=1.0, inflow_vel=inflow_vel,
+                    use_wall=True, wall_phi=phi, obs_vel=zero)
+            b[0], b[1], b[2], b[3], b[4], b[5] = b[1], b[0], b[3], b[2], b[5], b[4]
+        out["c3_cylinder_8192"] = entry(_event_ms(cyl_step, K, 3, barrier, world, device), H * W, 72.0,
+                                        f"demo_2d_LBM_cylinder.py scaled to {H}x{W} (D = {D}): MRT, moving-wall step, INFLOW / OUTFLOW rows, "
+                                        "contact-angle ring, rho / u read and stored every step (+24 B per cell not counted)")
+        del b, f0, zero, cflags, phi, crho, cvel
+        torch.cuda.empty_cache()
+    # C4 scaled: concentration step on the scaled tip geometry, row slabs at N > 1
+    G = G2
+    P = SimulationParameters(simulation_size=(1, 1, G, G), device=device, contact_angle=None, axisymmetric_type=1)
+    R = SimulationRunner(P)
+    fs = R.create_fused_step(operator="bgk", is_convection=True, tau_D=1.0)
+    row0, nrows = jrl_slab.slab_rows(G, world, rank)
+    rows = torch.arange(row0 - 1, row0 + nrows + 1) % G if world > 1 else torch.arange(G)
+    flags, mesh, phi, vel, C = WL.c4_state(device, G, G, rows, G // 128)
+    h = R.create_collision().get_feq_(dx=1.0, dt=1.0, rho=C, vel=torch.zeros_like(vel))
+    kw = dict(phi_obs=phi, mesh_grid=mesh, inflow_density=0, clamp01=True)
+    if world > 1:
+        lat = jrl_slab.SlabLattice(fs, G, G, rank=rank, world=world, device=device)
+        lat.set_state(h, flags=flags, rho=C, vel=vel, **kw)
+        Cout = torch.empty_like(C)
+
+        def c4_step():
+            lat.step(store_moments=True, rho_out=Cout)
+    else:
+        st = [h, torch.empty_like(h), C, torch.empty_like(C)]
+
+        def c4_step():
+            fs.step(st[0], flags, st[2], vel, f_out=st[1], rho_out=st[3], **kw)
+            st[0], st[1], st[2], st[3] = st[1], st[0], st[3], st[2]
+    out["c4_conc_scaled"] = entry(_event_ms(c4_step, K, 3, barrier, world, device), nrows * G, 84.0,
+                                  f"demo_2d_LBM_JRL_C_cylinder.py scaled to {G}^2 (tip radius 6.5 x {G // 128}, x-axis symmetry, is_negative layout): "
+                                  "fused concentration step, static tip, analytic stand-in velocity; 72 B h + 8 B u read + 4 B C write",
+                                  decomposition="row slabs, ring halo exchange (NCCL)" if world > 1 else "single domain", n_gpus=world)
+    return out
 
 
 def run_reference_arm(args):
@@ -326,18 +508,33 @@ def main():
         torch.cuda.synchronize()
 
     wl = Workload(G, rank, world, device)
-    for _ in range(Wm):
-        wl.step()
-    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches0 = jrl_native.launch_count
     with ClockSampler(local) as clocks:
         barrier()
+        e0.record()
+        for _ in range(max(Wm, 1)):
+            wl.step()
+        e1.record()
+        barrier()
+        # untimed pre-roll: PRE_ROLL_S of the same steps, so that the timed region starts with the GPU at its
+        # under-load clocks and the sampler has a load window around it (same count on every rank: slabs exchange halos)
+        pre = torch.tensor([PRE_ROLL_S * 1e3 / max(e0.elapsed_time(e1) / max(Wm, 1), 1e-3)], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(pre, op=dist.ReduceOp.MAX)
+        pre = int(min(5000, max(0, math.ceil(float(pre.item())) - max(Wm, 1))))
+        for i in range(pre):
+            wl.step()
+            if i % 32 == 31:
+                torch.cuda.synchronize()
+        barrier()
+        launches0 = jrl_native.launch_count
+        clocks.mark()
         e0.record()
         for _ in range(K):
             wl.step()
         e1.record()
         barrier()
+        clocks.mark()
     launches = jrl_native.launch_count - launches0
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
     nl = torch.tensor([launches], dtype=torch.int64, device=device)
@@ -358,7 +555,7 @@ def main():
 
     e2e = None
     if not args.no_e2e:
-        sec, h2d, d2h, hs = run_e2e(wl, K, Wm, device, barrier)
+        sec, h2d, d2h, hs = run_e2e(wl, K, Wm, device, barrier, full_flags=args.e2e_full_flags)
         agg = torch.tensor([sec, float(h2d), float(d2h)], dtype=torch.float64, device=device)
         mass_steps = hs[:, 0].to(device)
         if world > 1:
@@ -372,9 +569,11 @@ def main():
             raise SystemExit(f"bench.py: e2e per-step mass read back from the device is off by {worst:.3e}")
         e2e = {"value": G * G * K / float(agg[0].item()) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(agg[1].item()),
                "d2h_bytes_per_step": int(agg[2].item()), "ms_per_step": float(agg[0].item()) / K * 1e3,
-               "what": "FusedStep/SlabLattice API; per step: H2D of the step's uint8 flags field from pinned host memory "
-                       "(prefetched one step ahead on a copy stream), one fused launch, D2H of the in-kernel mass/momentum "
-                       "sums (checked on the host: mass conserved to %.1e)" % worst}
+               "what": ("FusedStep/SlabLattice API; per step: H2D of the step's dirty flag rows (a %d-row band of the host-owned uint8 "
+                        "flags field that moves one row per step, pinned memory -> device flags)" % E2E_BAND_ROWS if not args.e2e_full_flags
+                        else "FusedStep/SlabLattice API; per step: H2D of the whole uint8 flags field from pinned host memory")
+                       + ", tile-mask rebuild, one fused launch, D2H of the in-kernel mass/momentum sums (checked on the host: "
+                         "mass conserved to %.1e)" % worst}
 
     peak, peak_src = measured_peak()
     traffic = None
@@ -395,9 +594,14 @@ def main():
             "config": {"workload": f"demo_2d_LBM.py double shear layer, D2Q9 BGK, periodic, {G}x{G} fp32 (BASELINE configs[4] strong-scaling grid)",
                        "grid": G, "tau": shear_tau(G), "rows_per_rank": wl.nrows, "decomposition": "row slabs, ring halo exchange (NCCL)" if world > 1 else "single domain",
                        "moments_stored_every": OUT_EVERY,
-                       "flags": "static all-FLUID field; its packed tile mask (jrl_tile_mask_u8) is built once in the value leg and rebuilt every step in the e2e leg (flags re-uploaded)",
+                       "flags": "static all-FLUID field; its packed tile mask (jrl_tile_mask_u8) is built once in the value leg and rebuilt every step in the e2e leg (dirty rows re-uploaded)",
                        "l2": "working set (2 x %.1f GB of populations per rank) is far larger than the 126 MB L2" % (36.0 * G * G / world / 1e9)},
             "roofline": roofline, "e2e": e2e, "gpu_launches": int(nl.item()), "mass_drift": mass_rel}
+    line["config"]["pre_roll_steps"] = pre
+    if not args.no_configs:
+        del wl
+        torch.cuda.empty_cache()
+        line["configs"] = extra_configs(device, rank, world, barrier, peak, G2=min(8192, G))
     if rank == 0:
         line["clocks"] = clocks.summary()
         if not args.no_cpu_baseline and world == 1:

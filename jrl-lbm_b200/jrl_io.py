@@ -37,6 +37,14 @@ def _npz_path(filename):
     return filename + ".npz"
 
 
+def _is_npz(filename):
+    try:
+        with open(filename, "rb") as f:
+            return f.read(2) == b"PK"
+    except OSError:
+        return False
+
+
 def fields_exist(filename):
     """True if a cache written by `save_fields` (either container) is present: the demos' `os.path.exists` test."""
     return (HAVE_H5PY and os.path.exists(filename)) or os.path.exists(_npz_path(filename))
@@ -63,8 +71,10 @@ def load_fields(filename, names=None, device=None, dtype=None):
     if HAVE_H5PY and os.path.exists(filename):
         with h5py.File(filename, "r") as f:
             data = {k: np.asarray(f[k]) for k in (names or f.keys())}
-    elif os.path.exists(_npz_path(filename)):
-        with np.load(_npz_path(filename)) as z:
+    elif os.path.exists(_npz_path(filename)) or _is_npz(filename):
+        # `<name>.h5.npz` (save_fields without h5py), or an .npz container AT the requested path: what the demos
+        # themselves write through the h5py stand-in used where h5py is not installed (tests/standins/h5py.py)
+        with np.load(filename if _is_npz(filename) else _npz_path(filename)) as z:
             data = {k: z[k] for k in (names or z.files)}
     else:
         raise FileNotFoundError("no field cache at {} (or {})".format(filename, _npz_path(filename)))

@@ -60,10 +60,14 @@ class RefKernels:
         L.jrl_ref_macro.argtypes = [i32, f64, f64, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32]
         L.jrl_ref_wall.argtypes = [i32, f64, f64, f64, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32]
         L.jrl_ref_num_threads.restype = i32
+        L.jrl_ref_set_num_threads.argtypes = [i32]
 
     @property
     def num_threads(self) -> int:
         return int(self.lib.jrl_ref_num_threads())
+
+    def set_num_threads(self, n: int) -> None:
+        self.lib.jrl_ref_set_num_threads(int(n))
 
     @staticmethod
     def _isd(a) -> int:

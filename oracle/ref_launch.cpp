@@ -173,6 +173,16 @@ int jrl_ref_wall(int is_double, double dt, double dx, double tau, const void *rh
     return 0;
 }
 
+void jrl_ref_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0)
+        omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int jrl_ref_num_threads(void)
 {
     int n = 1;

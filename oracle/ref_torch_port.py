@@ -60,10 +60,11 @@ class ReferenceCpuLoop:
     """demo_2d_LBM.py:101-119 loop body on CPU tensors."""
 
     def __init__(self, tau, threads=None):
-        if threads:
-            torch.set_num_threads(threads)
         self.tau = tau
         self.ker = ref_cpu.RefKernels()
+        if threads:
+            torch.set_num_threads(threads)
+            self.ker.set_num_threads(threads)   # the OpenMP runtime of libjrl_ref.so (OMP_NUM_THREADS may be 1 under torchrun)
 
     @property
     def cores(self):

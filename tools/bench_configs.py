@@ -20,6 +20,7 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "jrl-lbm_b200")); sys.path.append(os.path.join(ROOT, "tests"))  # tests/jrl_scenarios.py: the demo loop bodies
 sys.path.insert(1, ROOT)
+sys.path.insert(2, os.path.join(ROOT, "tools"))
 
 import torch  # noqa: E402
 
@@ -118,32 +119,8 @@ def big_cases(S, api, dev, G):
 
 
 def c4_state(api, S, dev, H, W, rows, refine):
-    """Scaled C4: tip radius 6.5 x refine, inflow height 20.5 x refine, Rg = 4, x-axis
-    symmetry, is_negative layout (demo_2d_LBM_JRL_C_cylinder.py:151-161 with the `refine` semantics of
-    demo_2d_LBM_JRL_C_ethaline.py:79-89), tip at its start position, analytic stand-in velocity.
-    Built for the global rows `rows` (wrapped LongTensor) so a slab never materialises the whole grid."""
-    radius_obs = 6.0 * refine + 0.5
-    inflow_height = 20.5 * refine
-    Rg_radius = int(4 * radius_obs + 0.5)
-    hi = int(inflow_height + 0.5)
-    ri = int(radius_obs + 0.5)
-    y = rows.to(dev).view(-1, 1)
-    x = torch.arange(W, device=dev).view(1, -1)
-    fl = torch.full((rows.numel(), W), 1, dtype=torch.uint8, device=dev)
-    fl[(y == 0).expand_as(fl) & (x >= 1)] = 16
-    fl[(y == H - 1).expand_as(fl)] = 2
-    fl[(x == W - 1).expand_as(fl) & (y < H - 1)] = 32
-    fl[(y == 0).expand_as(fl) & (x >= Rg_radius)] = 32
-    fl[(y < hi) & (x < Rg_radius)] = 2
-    fl[(y == hi - 1) & (x < ri)] = 8
-    mesh = torch.stack([(x + 0.5).expand(rows.numel(), W), (y + 0.5).expand(rows.numel(), W)]).unsqueeze(0).float().contiguous()
-    box_radius = Rg_radius + 100.0
-    phi = torch.maximum(mesh[:, 0:1] - (Rg_radius - box_radius) - box_radius, mesh[:, 1:2] - (inflow_height - box_radius) - box_radius)
-    phi = torch.minimum(phi, -(mesh[:, 1:2] - H)).contiguous()
-    vel = (S.analytic_tip_velocity(mesh, inflow_height, radius_obs) * 0.05).contiguous()
-    C = torch.ones((1, 1, rows.numel(), W), device=dev)
-    C[0, 0][fl == 2] = 0.0
-    return fl.view(1, 1, -1, W).contiguous(), mesh, phi, vel, C
+    import workloads
+    return workloads.c4_state(dev, H, W, rows, refine)
 
 
 def c4_big(S, api, dev, G):
