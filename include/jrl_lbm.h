@@ -53,6 +53,12 @@ int jrl_stream_f32(const uint8_t *flags, const float *f, const float *phi_obs, f
                    float *rho, float *vel, const float *inflow_vel, double inflow_density,
                    int axisym, int B, int H, int W, void *stream);
 
+/* The in-place side effects of streaming alone (propagation.cu:300, 320-321, 362): rho = inflow_density (when >= 0)
+ * and vel = inflow_vel (when given) at INFLOW cells, rho = 1 at INFLOW_2 cells.  jrl_step_f32 leaves the
+ * previous-step rho / vel untouched; the host layer issues this launch when the caller still holds those tensors. */
+int jrl_inflow_apply_f32(const uint8_t *flags, float *rho, float *vel, const float *inflow_vel, double inflow_density,
+                         int B, int H, int W, void *stream);
+
 /* prop.rebounce_obstacle, LBM_propagation_2d.py:181-186 */
 int jrl_rebounce_f32(const float *f, const uint8_t *flags, float *f_new, int B, int H, int W, void *stream);
 

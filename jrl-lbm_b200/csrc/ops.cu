@@ -47,6 +47,30 @@ __global__ void __launch_bounds__(kThreads) k_rebounce(Grid g, const float *__re
         o[q * g.HW] = s[(obs ? opp(q) : q) * g.HW];
 }
 
+// Streaming's in-place side effects alone (propagation.cu:300, 320-321, 362): rho = inflow_density and
+// vel = inflow_vel at INFLOW cells, rho = 1 at INFLOW_2 cells.  The fused step never mutates the previous-step
+// fields (lattice.cuh stream_cell<.., WRITE = false>); a caller that still holds them after a fused step gets the
+// reference's mutation from this launch.
+__global__ void __launch_bounds__(kThreads) k_inflow_apply(Grid g, const uint8_t *__restrict__ flags, float *rho, float *vel,
+                                                           const float *__restrict__ inflow_vel, int has_density, float density)
+{
+    pdl_enter();
+    JRL_CELL_PROLOGUE
+    const uint8_t me = flags[b * g.HW + i];
+    if (me == CT_INFLOW)
+    {
+        if (rho != nullptr && has_density)
+            rho[b * g.HW + i] = density;
+        if (vel != nullptr && inflow_vel != nullptr)
+        {
+            vel[b * 2 * g.HW + i] = inflow_vel[0];
+            vel[b * 2 * g.HW + g.HW + i] = inflow_vel[1];
+        }
+    }
+    else if (me == CT_INFLOW_2 && rho != nullptr)
+        rho[b * g.HW + i] = 1.f;
+}
+
 // ---- R2 / R7 ---------------------------------------------------------------------------------
 // mode 0: LBMMacroCompute2d.macro_compute (torch-op path); mode 1: kernel_macompute_2d_forward
 template <int MODE>
@@ -656,6 +680,18 @@ int jrl_rebounce_f32(const float *f, const uint8_t *flags, float *f_new, int B, 
     JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
     const Grid g = make_grid(H, W, 0);
     JRL_LAUNCH(k_rebounce, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, f, flags, f_new);
+    return check_launch(fn);
+}
+
+int jrl_inflow_apply_f32(const uint8_t *flags, float *rho, float *vel, const float *inflow_vel, double inflow_density, int B,
+                         int H, int W, void *stream)
+{
+    const char *fn = "jrl_inflow_apply_f32";
+    JRL_REQUIRE(flags && (rho || vel), fn, "flags and at least one of rho / vel required");
+    JRL_REQUIRE(dims_ok(B, H, W), fn, "bad dimensions");
+    const Grid g = make_grid(H, W, 0);
+    JRL_LAUNCH_PDL(k_inflow_apply, cell_grid(g, B), kThreads, (cudaStream_t)stream, g, flags, rho, vel, inflow_vel,
+                   inflow_density >= 0.0 ? 1 : 0, (float)inflow_density);
     return check_launch(fn);
 }
 

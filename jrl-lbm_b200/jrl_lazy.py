@@ -151,7 +151,9 @@ class PendingStep:
     def check_unmodified(self):
         for t, v in self._watch:
             if t._version != v:
+                names = [n for n in ("f_in", "flags", "phi_obs", "rho_in", "vel_in", "inflow_vel") if getattr(self, n) is t]
                 raise RuntimeError(
+                    f"[{', '.join(names) or 'a later argument'}: version {v} -> {t._version}] "
                     "JRL-LBM-B200: a tensor passed to propagation() / solve_boundary() / macro_compute() was modified "
                     "in place before the step was launched; the deferred step cannot be replayed.  Set JRL_LBM_FUSE=0 "
                     "to launch every call immediately.")
@@ -222,6 +224,16 @@ class PendingStep:
         populations were never stored (their handles replay eagerly if anyone still looks at them)."""
         self.launched = True
         stats["fused"] += 1
+        # jrl_step_f32 does not write the previous-step rho / vel; if the caller still holds the tensors propagation()
+        # returned for them, give them streaming's in-place writes now (one small launch; the demos rebind both names
+        # before collision(), so for them this never runs)
+        alive = [r for r in ("rho_in", "vel_in") if r in self.handles and self.handles[r]() is not None
+                 and self.handles[r]()._real is None]
+        if alive:
+            self.prop._inflow_apply(self.flags, self.rho_in if "rho_in" in alive else None,
+                                    self.vel_in if "vel_in" in alive else None, self.inflow_vel, self.inflow_density)
+            for r in alive:
+                self._publish(r, self.rho_in if r == "rho_in" else self.vel_in)
         if self.moments["kind"] == "C":
             # with the clamp fused in, the unclamped sum was never stored: its handle replays eagerly if touched
             self._publish("C_clamp" if self.clamp else "C", rho_out)

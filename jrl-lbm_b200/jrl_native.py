@@ -79,6 +79,7 @@ PROTOTYPES = {
     "jrl_version": [],
     "jrl_last_error": [],
     "jrl_stream_f32": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _i, _i, _i, _i, _vp],
+    "jrl_inflow_apply_f32": [_vp, _vp, _vp, _vp, _d, _i, _i, _i, _vp],
     "jrl_rebounce_f32": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "jrl_moments_f32": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _d, _i, _i, _i, _vp],
     "jrl_moments_kernel_f32": [_vp, _vp, _vp, _vp, _vp, _vp, _d, _i, _i, _i, _vp],

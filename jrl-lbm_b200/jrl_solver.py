@@ -102,7 +102,10 @@ class LBMPropagation2d:
         f_new = P.handle("f_stream", f.shape, f)
         if inflow_info:
             r = torch.Tensor([]) if rho is None else (P.handle("rho_in", rho.shape, rho) if rho.numel() else rho)
-            v = torch.Tensor([]) if vel is None else (P.handle("vel_in", vel.shape, vel) if vel.numel() else vel)
+            # vel is only written at INFLOW cells when inflow_vel is given (propagation.cu:318-321): otherwise it IS
+            # the caller's tensor, nothing pending
+            v = torch.Tensor([]) if vel is None else (
+                P.handle("vel_in", vel.shape, vel) if (vel.numel() and P.inflow_vel is not None) else vel)
             return (r, v, f_new)
         return f_new
 
@@ -119,6 +122,16 @@ class LBMPropagation2d:
         N.call("jrl_stream_f32", p_flags, p_f, p_phi, ctypes.c_void_p(f_new.data_ptr()), p_rho, p_vel, p_iv,
                -1.0 if inflow_density is None else float(inflow_density), self.axisymmetric_type, B, H, W, like=f)
         return f_new
+
+    def _inflow_apply(self, flags, rho, vel, inflow_vel, inflow_density):
+        """Streaming's in-place writes to rho / vel alone (jrl_inflow_apply_f32)."""
+        like = rho if rho is not None else vel
+        B, H, W = _dims(like, "rho")
+        N.call("jrl_inflow_apply_f32", N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=like),
+               N.tensor_ptr(rho, "rho", shape=(B, 1, H, W), like=like, optional=True),
+               N.tensor_ptr(vel, "vel", shape=(B, 2, H, W), like=like, optional=True),
+               N.tensor_ptr(inflow_vel, "inflow_vel", shape=(2,), like=like, optional=True),
+               -1.0 if inflow_density is None else float(inflow_density), B, H, W, like=like)
 
     def rebounce_obstacle(self, f, flags):
         """OBSTACLE cells get their populations reversed (LBM_propagation_2d.py:181-186)."""
