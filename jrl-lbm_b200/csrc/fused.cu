@@ -1017,7 +1017,14 @@ static int launch_step(const StepArgs &a, int B, cudaStream_t s)
     else if (a.cp.op == OP_MRT)
         JRL_STEP(OP_MRT, 0);
     else
-        JRL_STEP(OP_KBC, 0);
+        switch (kbc_index_of(a.cp.kbc_type))  // one instantiation per KBC variant (lattice.cuh OP_KBC_T0)
+        {
+        case 1: JRL_STEP(OP_KBC_T0 + 1, 0); break;
+        case 2: JRL_STEP(OP_KBC_T0 + 2, 0); break;
+        case 3: JRL_STEP(OP_KBC_T0 + 3, 0); break;
+        case 4: JRL_STEP(OP_KBC_T0 + 4, 0); break;
+        default: JRL_STEP(OP_KBC_T0 + 0, 0); break;
+        }
 #undef JRL_STEP
     return 0;
 }

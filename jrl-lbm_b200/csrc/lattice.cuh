@@ -26,6 +26,12 @@ enum : int { AXI_NOT = 0, AXI_X = 1, AXI_Y = 2 };
 // utils/types.py:18-23
 enum : int { KBC_LBGK = 0, KBC_A = 0x85, KBC_B = 0x86, KBC_C = 0x89, KBC_D = 0x8A };
 enum : int { OP_BGK = 0, OP_MRT = 1, OP_KBC = 2 };
+// Template values OP_KBC_T0 + i select KBC with the variant known at compile time (i: 0 LBGK, 1 A, 2 B, 3 C, 4 D), which
+// removes the run-time select chains and the dead central-moment code of the other variants from the hot kernels
+// (~100 instructions per cell of ~940); OP_KBC itself keeps the run-time dispatch on p.kbc_type.
+enum : int { OP_KBC_T0 = 16 };
+__host__ __device__ constexpr int kbc_code_of(int i) { return i == 0 ? KBC_LBGK : (i == 1 ? KBC_A : (i == 2 ? KBC_B : (i == 3 ? KBC_C : KBC_D))); }
+inline int kbc_index_of(int code) { return code == KBC_A ? 1 : (code == KBC_B ? 2 : (code == KBC_C ? 3 : (code == KBC_D ? 4 : 0))); }
 
 // propagation.cu:9-20, 49-64: rest, +x, +y, -x, -y, ++, -+, --, +-
 #define JRL_EX(q) ((q) == 1 || (q) == 5 || (q) == 8 ? 1 : ((q) == 3 || (q) == 6 || (q) == 7 ? -1 : 0))
@@ -360,11 +366,27 @@ struct EqParams
     float inv_cs2;  // (float)(1/cs2): torch divides by a python scalar as a reciprocal multiply
 };
 
+// a / b with IEEE bits, keeping EXACT-ZERO numerators off the division's slow path.  nvcc's fp32 division is a
+// reciprocal + Newton sequence guarded by FCHK, which sends zero / denormal / huge operands to a ~60-instruction
+// subroutine (CALL); with a zero numerator in one lane the whole warp waits for it.  Lattice states are full of exact
+// zeros (a force field of zeros, u = 0 during the concentration balance phase, f - feq = 0 in the saturated parts
+// of a shear layer: ncu showed 7 CALLs per cell in the KBC kernel, profiles/r1_kstep_vec4_kbc_details.txt), and
+// the quotient is then known: (+-0) / b = +-0 with the XOR of the signs for every b except 0 and NaN, which give NaN.
+// The division itself is fed a harmless numerator in those lanes and its result discarded, so the bits never change.
+__device__ __forceinline__ float div_ieee(float a, float b)
+{
+    const bool az = a == 0.f;
+    const float q = (az ? 1.f : a) / b;
+    const float z = __int_as_float(__float_as_int(a) ^ (__float_as_int(b) & (int)0x80000000));  // +-0, sign(a) ^ sign(b)
+    const bool nan = (b != b) | (b == 0.f);
+    return az ? (nan ? __int_as_float(0x7fffffff) : z) : q;
+}
+
 __device__ __forceinline__ void half_force_shift(float rho, float &ux, float &uy, float fx, float fy)
 {
     // LBM_collision_2d.py:246-250: u += where(rho <= 1e-10, 0, 0.5 * force / rho)
-    const float ax = rho <= 1e-10f ? 0.f : (0.5f * fx) / rho;
-    const float ay = rho <= 1e-10f ? 0.f : (0.5f * fy) / rho;
+    const float ax = rho <= 1e-10f ? 0.f : div_ieee(0.5f * fx, rho);
+    const float ay = rho <= 1e-10f ? 0.f : div_ieee(0.5f * fy, rho);
     ux = ux + ax;
     uy = uy + ay;
 }
@@ -436,10 +458,11 @@ __device__ __forceinline__ float dot9_cublas(const float *a, const float *x)
 }
 
 // Entropic KBC relaxation, LBM_collision_KBC_2d.py:70-249.  Returns Omega in om[].
+template <int KT = -1>
 __device__ __forceinline__ void kbc_omega(const CollideParams &p, float rho, float ux, float uy,
                                           const float f[9], const float feq[9], float om[9])
 {
-    const int type = p.kbc_type;
+    const int type = KT < 0 ? p.kbc_type : KT;
     if (type == KBC_LBGK)
     {
         // ds = f - feq, dh = 0, gamma = 2: Omega = -beta * (2 ds + 2 * 0)
@@ -526,11 +549,11 @@ __device__ __forceinline__ void kbc_omega(const CollideParams &p, float rho, flo
         ds[q] = s[q] - se[q];
         dh[q] = (f[q] - feq[q]) - ds[q];
         const float den = feq[q] + eps;
-        a[q] = (ds[q] * dh[q]) / den;
-        b[q] = (dh[q] * dh[q]) / den;
+        a[q] = div_ieee(ds[q] * dh[q], den);
+        b[q] = div_ieee(dh[q] * dh[q], den);
     }
     const float dsdh = sum9(a), dhdh = sum9(b);  // `.sum(dim=1, keepdim=True)` (:240-241): torch-CUDA order
-    const float gamma = p.inv_beta - p.two_m_inv_beta * (dsdh / (dhdh + eps));
+    const float gamma = p.inv_beta - p.two_m_inv_beta * div_ieee(dsdh, dhdh + eps);
 #pragma unroll
     for (int q = 0; q < 9; ++q)
         om[q] = -p.beta * (2.f * ds[q] + gamma * dh[q]);
@@ -550,7 +573,7 @@ __device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, 
                                              bool has_force, float fx, float fy, float r,
                                              const float *G, float f[9])
 {
-    const int op = OP < 0 ? p.op : OP;
+    const int op = OP < 0 ? p.op : (OP >= OP_KBC_T0 ? (int)OP_KBC : OP);
     const float ux_raw = ux, uy_raw = uy;  // the KBC moments use the unshifted velocity (LBM_collision_KBC_2d.py:295-305)
     if (has_force)
         half_force_shift(rho, ux, uy, fx, fy);
@@ -564,7 +587,7 @@ __device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, 
             // The reference divides per direction, (k e_qx) / r.  e_qx is +1, -1 or 0 and IEEE division is
             // sign-symmetric, so three quotients give the same bits: k/r, -(k/r), and (k 0)/r = 0 for every
             // finite non-zero r (NaN for r = 0 or NaN, kept).
-            const float ur_r = (-ux) / r;
+            const float ur_r = div_ieee(-ux, r);
             const float w1 = p.conv_k1 / r, s1 = p.conv_k2 / r;
             const float z = (r == 0.f || r != r) ? 0.f / r : 0.f;
 #pragma unroll
@@ -581,7 +604,7 @@ __device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, 
         {
             // LBM_collision_2d.py:428-436: G = w_q * A1, A1 = -rho u_z / r', uniform omega
             // (the per-direction branch for the y axis is unreachable, :522).  r here is r'.
-            const float a1 = ((-rho) * uy) / r;
+            const float a1 = div_ieee((-rho) * uy, r);
 #pragma unroll
             for (int q = 0; q < 9; ++q)
                 f[q] = (f[q] + p.omega * (feq[q] - f[q])) + p.dt * (a1 * weight(q));
@@ -606,7 +629,7 @@ __device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, 
             om[i] = dot9_cublas(p.mrt + i * 9, d);
     }
     else
-        kbc_omega(p, rho, ux_raw, uy_raw, f, feq, om);
+        kbc_omega<(OP >= OP_KBC_T0 ? kbc_code_of(OP - OP_KBC_T0) : -1)>(p, rho, ux_raw, uy_raw, f, feq, om);
 #pragma unroll
     for (int q = 0; q < 9; ++q)
         f[q] = (f[q] + om[q]) + (G ? p.dt * G[q] : 0.f);

@@ -104,7 +104,7 @@ __device__ __forceinline__ void axisym_fluid_source(const SourceParams &p, const
     if (p.axisym == AXI_X)
     {
         const float r = mesh[self];
-        const float A1 = ((-rho0) * ux) / r;
+        const float A1 = div_ieee((-rho0) * ux, r);
         const float mu = p.visc * rho0;
         // A2 = (d_r(rho cs2) + div(rho u_r u)) * dt / (2 r)
         float pr[9], ax[9], ay[9], a1n[9];
@@ -115,7 +115,7 @@ __device__ __forceinline__ void axisym_fluid_source(const SourceParams &p, const
             const float ru = rh[q] * vx[q];
             ax[q] = ru * vx[q];
             ay[q] = ru * vy[q];
-            a1n[q] = ((-rh[q]) * vx[q]) / mesh[s.at[q]];
+            a1n[q] = div_ieee((-rh[q]) * vx[q], mesh[s.at[q]]);
         }
         float gpx, gpy, ga1x, ga1y;
         grad_sums(s, pr, gpx, gpy);
@@ -126,7 +126,7 @@ __device__ __forceinline__ void axisym_fluid_source(const SourceParams &p, const
         const float dv = me_obs ? 0.f : div12(div_sum(ax, ay), p.twelve_dx);
         float A2 = gpx + dv;
         A2 = A2 * (p.dt / (2.f * r));
-        float F2x = (mu / r) * (gux - ux / r);
+        float F2x = (mu / r) * (gux - div_ieee(ux, r));
         float F2y = (mu / r) * gvx;
         F2x = F2x + ux * A1;
         F2y = F2y + uy * A1;
@@ -145,10 +145,10 @@ __device__ __forceinline__ void axisym_fluid_source(const SourceParams &p, const
         float r = mesh[g.HW + self] - p.half_dx;
         if (y == 0)
             r = 1.f;
-        const float A1 = ((-rho0) * uy) / r;
+        const float A1 = div_ieee((-rho0) * uy, r);
         const float mu = p.visc * rho0;
-        const float H1 = (mu * (guy + gvx)) / r - ((rho0 * ux) * uy) / r;
-        const float H2 = ((mu * (gvy * 2.f)) / r - ((2.f * mu) * uy) / (r * r)) - ((rho0 * uy) * uy) / r;
+        const float H1 = div_ieee(mu * (guy + gvx), r) - div_ieee((rho0 * ux) * uy, r);
+        const float H2 = (div_ieee(mu * (gvy * 2.f), r) - div_ieee((2.f * mu) * uy, r * r)) - div_ieee((rho0 * uy) * uy, r);
 #pragma unroll
         for (int q = 0; q < 9; ++q)
         {

@@ -5,6 +5,9 @@
 // where no GPU exists.  The product never loads it: jrl_native.load() only ever opens the nvcc
 // build, and raises when that is missing.
 #pragma once
+#include <cstring>
+static inline int __float_as_int(float x) { int i; std::memcpy(&i, &x, 4); return i; }
+static inline float __int_as_float(int i) { float x; std::memcpy(&x, &i, 4); return x; }
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
