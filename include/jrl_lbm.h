@@ -193,6 +193,10 @@ typedef struct jrl_step_desc
     const float *wall_phi;  /* phi_obs seen by the moving-wall step; NULL: same as phi_obs.
                                (demo_2d_LBM_cylinder.py:139-157 streams WITHOUT phi_obs -- plain halfway
                                bounce-back -- but passes phi_obs to solve_boundary) */
+    void *worklist;           /* NULL, or `worklist_bytes` of device scratch (4-byte aligned; jrl_worklist_bytes gives a
+                                 sufficient size): the pipelined kernel defers its boundary groups to a second launch
+                                 through it.  Contents are meaningless between calls. */
+    long long worklist_bytes;
     const uint8_t *tile_mask; /* NULL, or the packed summary of `flags` written by jrl_tile_mask_u8 for exactly
                                these flags (same B, stored rows, W): lets the pipelined kernel skip the flag
                                rows of all-FLUID tiles.  Results are identical with and without it; it must be
@@ -218,6 +222,9 @@ int jrl_run_f32(const jrl_step_desc *d, int nsteps, int store_every, long long s
  * slab_rows + 2).  jrl_tile_mask_bytes returns the size of `mask` in bytes (0 on bad arguments).
  * Needs W % 16 == 0 and 16-byte aligned flags (the pipelined kernel's own requirements). */
 int jrl_tile_mask_bytes(int B, int Hs, int W);
+/* Size in bytes of the scratch jrl_step_desc.worklist may point to: room for every boundary group of a grid in which
+ * up to 1/8 of the groups are boundary groups (groups beyond the capacity are simply computed in place). */
+long long jrl_worklist_bytes(int B, int Hs, int W);
 int jrl_tile_mask_u8(const uint8_t *flags, uint8_t *mask, int B, int Hs, int W, void *stream);
 
 /* ---- device-side tip motion ----------------------------------------------------

@@ -46,6 +46,8 @@ struct StepArgs
     const float *wall_phi;
     const uint8_t *tile_mask;  // [B][stored rows][mask_tpr] from jrl_tile_mask_u8, or nullptr
     int mask_tpr;
+    unsigned *worklist;        // [2 + cap]: [0] = entries appended by this launch, [2..] = (tile, thread) of deferred groups
+    unsigned worklist_cap;
     double *sums;
     const float *rho;  // previous-step density / concentration (kept at OBSTACLE cells)
     const float *vel;  // previous-step velocity, or the advecting velocity when convection
@@ -847,11 +849,30 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
             }
             else
             {
-                const float4 r = step_group_generic<VEC, OP, CONV>(a, tl.b, y, x0);
-                acc[0] = r.x;
-                acc[1] = r.y;
-                acc[2] = r.z;
-                cells = r.w;
+                // A boundary group.  The generic rules are ~45 k instructions that the persistent CTAs would fetch
+                // cold and walk serially (measured: ~20 us per group, 8 consumer warps hiding nothing -- the 16 k
+                // boundary groups of the scaled C4 grid cost more than its 16.7 M bulk groups).  Defer it: append
+                // (tile, thread) to the work list and let k_step_worklist run all of them, one cell per thread, hot
+                // in the instruction cache and across the whole GPU, right after this kernel.  f_in is read-only
+                // and every group writes only its own cells of f_out, so the order does not matter.
+                bool deferred = false;
+                if (a.worklist != nullptr)
+                {
+                    const unsigned slot = atomicAdd(a.worklist, 1u);
+                    if (slot < a.worklist_cap)
+                    {
+                        a.worklist[2 + slot] = t * (unsigned)(CW / VEC) + (unsigned)tid;
+                        deferred = true;
+                    }
+                }
+                if (!deferred)
+                {
+                    const float4 r = step_group_generic<VEC, OP, CONV>(a, tl.b, y, x0);
+                    acc[0] = r.x;
+                    acc[1] = r.y;
+                    acc[2] = r.z;
+                    cells = r.w;
+                }
             }
         }
         if (a.sums)
@@ -859,17 +880,44 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
     }
 }
 
+// Second pass of the pipelined step: the boundary groups k_step_pipe deferred, one CELL per thread by the generic
+// rules (the same device functions as everywhere else: bit-identical results), grid-stride over the list.
+template <int OP, int CONV, int VEC>
+__global__ void __launch_bounds__(256) k_step_worklist(const __grid_constant__ StepArgs a, unsigned tpr, unsigned rows)
+{
+    const unsigned n = min(a.worklist[0], a.worklist_cap);
+    const unsigned long long cells_total = (unsigned long long)n * VEC;
+    float acc[3] = {0.f, 0.f, 0.f}, cells = 0.f;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < cells_total;
+         i += (unsigned long long)gridDim.x * blockDim.x)
+    {
+        const unsigned e = a.worklist[2 + i / VEC], k = (unsigned)(i % VEC);
+        const unsigned t = e / (unsigned)(CW / VEC), tid = e % (unsigned)(CW / VEC);
+        const Tile tl = tile_of(a, t, tpr, rows);
+        const float4 r = step_group_generic<1, OP, CONV>(a, tl.b, tl.y, tl.x0 + VEC * (int)tid + (int)k);
+        acc[0] += r.x;
+        acc[1] += r.y;
+        acc[2] += r.z;
+        cells += r.w;
+    }
+    if (a.sums)
+        add_sums(a.sums, acc, cells);
+}
+
 template <int OP, int CONV, int VEC, int STAGES, int MINB>
 static int launch_cfg(const StepArgs &a, unsigned total, unsigned tpr, unsigned rows, cudaStream_t s)
 {
     auto kern = k_step_pipe<OP, CONV, VEC, STAGES, MINB>;
     const size_t smem = sizeof(Stage<conv_rows(CONV)>) * STAGES;
-    static bool configured = false;  // per instantiation
-    if (!configured)
+    static unsigned long long configured = 0ull;  // per instantiation, one bit per device (a multi-GPU process)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 64 || !((configured >> dev) & 1ull))
     {
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
             return JRL_ERR_CUDA;
-        configured = true;
+        if (dev < 64)
+            configured |= 1ull << dev;
     }
     // CTA b works on tiles b, b + nb, b + 2 nb, ...: with nb coprime to the tiles per row every CTA visits every
     // tile column equally often, so a boundary that costs extra in one column (a side wall, an inlet, the
@@ -878,7 +926,15 @@ static int launch_cfg(const StepArgs &a, unsigned total, unsigned tpr, unsigned 
     auto gcd = [](unsigned x, unsigned y) { while (y) { const unsigned r = x % y; x = y; y = r; } return x; };
     while (nb > 1 && gcd(nb, tpr) != 1)
         --nb;
-    kern<<<nb, CW / VEC + 32, smem, s>>>(a, total, tpr, rows);
+    const bool defer = a.worklist != nullptr && total < (1u << 23);  // (tile, thread) packs into 32 bits
+    StepArgs b = a;
+    if (!defer)
+        b.worklist = nullptr;
+    else if (cudaMemsetAsync(a.worklist, 0, sizeof(unsigned), s) != cudaSuccess)
+        return JRL_ERR_CUDA;
+    kern<<<nb, CW / VEC + 32, smem, s>>>(b, total, tpr, rows);
+    if (defer)
+        k_step_worklist<OP, CONV, VEC><<<4 * sm_count(), 256, 0, s>>>(b, tpr, rows);
     return 0;
 }
 
@@ -916,8 +972,11 @@ static int launch(const StepArgs &a, int B, cudaStream_t s)
 #ifdef JRL_EXP_FAST_BUILD  // experiment builds (tools/): one operator only (JRL_EXP_FAST_OP, default BGK), compiles in a fraction of the time
     return launch_one<JRL_EXP_FAST_OP, 0>(a, total, tpr, rows, s);
 #else
+    // x-axis concentration form: three IEEE divisions and the per-direction relaxation per cell make it issue-bound
+    // with 8 consumer warps per SM; 2 cells per consumer thread and 3 stages, as for MRT (scaled C4 at 8192^2:
+    // 1.54 -> 1.32 ms; all-FLUID 1.39 -> 1.22 ms)
     if (a.cp.convection)
-        return a.g.axisym == AXI_X ? launch_one<OP_BGK, 1>(a, total, tpr, rows, s)
+        return a.g.axisym == AXI_X ? launch_cfg<OP_BGK, 1, 2, 3, JRL_PIPE_MINB>(a, total, tpr, rows, s)
                                    : (a.g.axisym == AXI_Y ? launch_one<OP_BGK, 2>(a, total, tpr, rows, s)
                                                           : launch_one<OP_BGK, 3>(a, total, tpr, rows, s));
     if (a.cp.op == OP_BGK)
@@ -1044,6 +1103,14 @@ extern "C" int jrl_tile_mask_bytes(int B, int Hs, int W)
     return n > 0x7fffffffll ? 0 : (int)n;
 }
 
+extern "C" long long jrl_worklist_bytes(int B, int Hs, int W)
+{
+    if (B < 1 || Hs < 1 || W < 1)
+        return 0;
+    const long long groups = (long long)B * Hs * ((W + 3) / 4);
+    return (long long)sizeof(unsigned) * (2 + std::max<long long>(4096, groups / 8));
+}
+
 extern "C" int jrl_tile_mask_u8(const uint8_t *flags, uint8_t *mask, int B, int Hs, int W, void *stream)
 {
     const char *fn = "jrl_tile_mask_u8";
@@ -1106,6 +1173,8 @@ static int step_once(const jrl_step_desc *d, void *stream)
     a.sums = d->sums;
     a.tile_mask = d->tile_mask;
     a.mask_tpr = (d->W + JRL_PIPE_CW - 1) / JRL_PIPE_CW;
+    a.worklist = d->worklist_bytes >= 3 * (long long)sizeof(unsigned) ? (unsigned *)d->worklist : nullptr;
+    a.worklist_cap = a.worklist ? (unsigned)std::min<long long>(d->worklist_bytes / (long long)sizeof(unsigned) - 2, 1ll << 30) : 0u;
     a.rho = d->rho;
     a.vel = d->vel;
     a.rho_out = d->rho_out;
@@ -1143,10 +1212,11 @@ static int step_once(const jrl_step_desc *d, void *stream)
     // with 2 cells per consumer thread (16 consumer warps per SM for the 81-FMA matvec: 4.7 TB/s at 8192^2 against
     // 4.1 in the register kernel and 3.95 with 4 cells per thread); KBC is bound by its instruction count (~940 per
     // cell, 19 IEEE divisions) and runs faster in the register kernel (1.6 vs 0.9-1.4 TB/s)
-    // (the concentration form on real geometries -- tip block, inlet column, symmetry axis -- has too many groups
-    // on the generic path for the pipelined kernel's eight consumer warps per SM: 3.4 ms vs 1.9 ms per step on
-    // the scaled C4 grid, so it also defaults to the register kernel; force_vec = 8 selects the pipeline)
-    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4 && (d->op == JRL_OP_BGK || d->op == JRL_OP_MRT) && !d->is_convection))
+    // The concentration form takes the pipeline too when the caller provides the work list through which boundary
+    // groups (tip block, inlet column, edge rows) are deferred to the second launch: scaled C4 grid 1.89 ms in the
+    // register kernel, 3.54 ms in the pipeline with the boundary groups computed in place, 1.32 ms with them deferred.
+    if (d->force_vec == 8 || (d->force_vec == 0 && vec == 4 && (d->op == JRL_OP_BGK || d->op == JRL_OP_MRT) &&
+                                (!d->is_convection || a.worklist != nullptr)))
     {
         const bool ok = vec == 4 && pipe::eligible(a, d->B);
         JRL_REQUIRE(ok || d->force_vec == 0, fn, "pipelined kernel needs W % 16 == 0, W >= 512 and 16-byte aligned planes");

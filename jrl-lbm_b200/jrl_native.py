@@ -44,7 +44,7 @@ class StepDesc(Structure):  # struct jrl_step_desc
                 ("mesh_grid", c_void_p), ("inflow_vel", c_void_p), ("inflow_density", c_double),
                 ("use_wall", c_int), ("obs_vel", c_void_p), ("slab_row0", c_int), ("slab_rows", c_int),
                 ("row_begin", c_int), ("row_end", c_int), ("force_vec", c_int), ("sums", c_void_p), ("wall_phi", c_void_p),
-                ("tile_mask", c_void_p)]
+                ("worklist", c_void_p), ("worklist_bytes", ctypes.c_longlong), ("tile_mask", c_void_p)]
 
 
 class TipDesc(Structure):  # struct jrl_tip_desc
@@ -95,6 +95,7 @@ PROTOTYPES = {
     "jrl_step_f32": [POINTER(StepDesc), _vp],
     "jrl_run_f32": [POINTER(StepDesc), _i, _i, ctypes.c_longlong, _vp],
     "jrl_tile_mask_bytes": [_i, _i, _i],
+    "jrl_worklist_bytes": [_i, _i, _i],
     "jrl_tile_mask_u8": [_vp, _vp, _i, _i, _i, _vp],
     "jrl_tip_prepare_conc_f32": [POINTER(TipDesc), _vp],
     "jrl_tip_prepare_fluid_f32": [POINTER(TipFluidDesc), _vp],
@@ -109,7 +110,7 @@ def _bind(lib):
     for name, argtypes in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the library lacks a declared symbol
         fn.argtypes = argtypes
-        fn.restype = c_char_p if name == "jrl_last_error" else c_int
+        fn.restype = c_char_p if name == "jrl_last_error" else (ctypes.c_longlong if name == "jrl_worklist_bytes" else c_int)
     return lib
 
 

@@ -57,6 +57,7 @@ class FusedStep:
         else:
             self.contact_tan = 0.0
         self.use_tile_mask = True
+        self._worklists = {}
         self._masks = {}  # id(flags) -> (weakref(flags), flags._version, mask tensor)
 
     def invalidate_masks(self):
@@ -151,12 +152,25 @@ class FusedStep:
         d.force_vec = int(force_vec)
         d.sums = N.tensor_ptr(sums, "sums", torch.float64, sums_shape or (N.SUM_SLOTS, 4), like=f, optional=True)
         d.wall_phi = N.tensor_ptr(wall_phi, "wall_phi", shape=(B, 1, Hs, W), like=f, optional=True)
-        mask = None
+        mask = wl = None
         if (self.use_tile_mask and W % 16 == 0 and W >= 512 and flags.data_ptr() % 16 == 0
-                and (force_vec == 8 or (force_vec == 0 and self.op in (N.OP_BGK, N.OP_MRT) and not self.is_convection))):
+                and (force_vec == 8 or (force_vec == 0 and self.op in (N.OP_BGK, N.OP_MRT)))):
             mask = self._tile_mask(flags, B, Hs, W)
+            wl = self._worklist(flags.device, B, Hs, W)
         d.tile_mask = None if mask is None else mask.data_ptr()
-        return d, f_out, rho_out, vel_out, (force, mask)
+        if wl is not None:
+            d.worklist, d.worklist_bytes = wl.data_ptr(), wl.numel() * 4
+        return d, f_out, rho_out, vel_out, (force, mask, wl)
+
+    def _worklist(self, device, B, Hs, W):
+        """Device scratch through which the pipelined kernel hands its boundary groups to the second launch
+        (jrl_step_desc.worklist); one buffer per device and extent, reused by every step."""
+        key = (str(device), B, Hs, W)
+        wl = self._worklists.get(key)
+        if wl is None:
+            n = int(N.load().jrl_worklist_bytes(B, Hs, W))
+            wl = self._worklists[key] = torch.zeros(((n + 3) // 4,), dtype=torch.int32, device=device)
+        return wl
 
     def run(self, f, flags, rho=None, vel=None, nsteps=1, *, f_alt=None, rho_alt=None, vel_alt=None, store_every=0,
             phi_obs=None, force=None, mesh_grid=None, inflow_vel=None, inflow_density=None, use_wall=False, obs_vel=None,

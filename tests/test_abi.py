@@ -24,7 +24,7 @@ def _header_text():
 def header_functions():
     """{name: number of parameters} of every function the header declares."""
     out = {}
-    for m in re.finditer(r"\b(?:int|const char \*)\s*(jrl_\w+)\s*\(([^;{]*?)\)\s*;", _header_text(), flags=re.S):
+    for m in re.finditer(r"\b(?:int|long long|const char \*)\s*(jrl_\w+)\s*\(([^;{]*?)\)\s*;", _header_text(), flags=re.S):
         args = m.group(2).strip()
         out[m.group(1)] = 0 if args in ("", "void") else len(args.split(","))
     return out

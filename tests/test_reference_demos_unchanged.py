@@ -27,6 +27,16 @@ from util import field_tol, rel_l2
 pytestmark = pytest.mark.skipif(D.demo_source_dir() is None, reason="reference demo scripts not available")
 
 
+# The cylinder stage A has an OUTFLOW row along the bottom edge next to the moving tip, and the reference's kernel
+# has a data race there (propagation.cu:195-255): on a B200 at 128 x 64 the racing reads of that row return
+# a MIX of the neighbour's old and new populations in 9 launches out of 10 (tools/exp_outflow_race.py,
+# profiles/r2_outflow_race.json; the right-hand OUTFLOW column, whose neighbour sits in the same warp, always reads the
+# new value).  The reference's CUDA run of this case therefore differs from its own CPU run by 2e-2 and is not
+# reproducible; the deterministic reading (neighbour's post-stream value = the CPU fixtures) is the pin for this pair.
+# The 45-degree and infinite-plane pairs, whose flows are insensitive to that row, match the CUDA run to 1e-6.
+REFCUDA_RACY = {"a_cylinder_g9", "b_cylinder_g9"}
+
+
 def _golden(name, refcuda=False):
     """demo_<name>.npz: written by the reference on the CPU (oracle/gen_golden_demos.py);
     demo_refcuda_<name>.npz: written by the reference's CUDA build on a B200 (tools/bench_ref_cuda.py).  The B200
@@ -34,7 +44,7 @@ def _golden(name, refcuda=False):
     differ from EACH OTHER by 7e-2 in u at step 1000 (1.5e-6 at step 100), so only a same-arithmetic comparison
     says anything there -- and this library reproduces the CUDA run of C1 bit for bit."""
     path = os.path.join(GOLDEN, f"demo_refcuda_{name}.npz")
-    if not (refcuda and os.path.exists(path)):
+    if not (refcuda and os.path.exists(path)) or name in REFCUDA_RACY:
         path = os.path.join(GOLDEN, f"demo_{name}.npz")
     if not os.path.exists(path):
         pytest.skip(f"golden {path} not generated")
