@@ -34,7 +34,11 @@ enum { JRL_OK = 0, JRL_ERR_ARG = -1, JRL_ERR_CUDA = -2 };
 enum { JRL_CELL_NOTHING = 0, JRL_CELL_FLUID = 1, JRL_CELL_OBSTACLE = 2, JRL_CELL_EMPTY = 4,
        JRL_CELL_INFLOW = 8, JRL_CELL_OUTFLOW = 16, JRL_CELL_INFLOW_2 = 32 };
 enum { JRL_AXI_NOT = 0, JRL_AXI_X = 1, JRL_AXI_Y = 2 };
-enum { JRL_OP_BGK = 0, JRL_OP_MRT = 1, JRL_OP_KBC = 2 };
+enum { JRL_OP_BGK = 0, JRL_OP_MRT = 1, JRL_OP_KBC = 2,
+       JRL_OP_NONE = 3 /* jrl_step_f32 only: stop before the collision -- f_out = the streamed (and wall-corrected)
+                          populations, rho_out / vel_out = their moments.  First half of the two-launch step of the
+                          axisymmetric FLUID form, whose source term needs the neighbours' post-stream moments
+                          (jrl_collide_f32 is the second half). */ };
 #define JRL_SUM_SLOTS 64
 enum { JRL_KBC_LBGK = 0, JRL_KBC_A = 0x85, JRL_KBC_B = 0x86, JRL_KBC_C = 0x89, JRL_KBC_D = 0x8A };
 

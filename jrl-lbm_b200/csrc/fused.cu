@@ -1075,6 +1075,8 @@ static int launch_step(const StepArgs &a, int B, cudaStream_t s)
         JRL_STEP(OP_BGK, 0);
     else if (a.cp.op == OP_MRT)
         JRL_STEP(OP_MRT, 0);
+    else if (a.cp.op == OP_NONE)
+        JRL_STEP(OP_NONE, 0);
     else
         switch (kbc_index_of(a.cp.kbc_type))  // one instantiation per KBC variant (lattice.cuh OP_KBC_T0)
         {
@@ -1134,14 +1136,17 @@ static int step_once(const jrl_step_desc *d, void *stream)
     JRL_REQUIRE(d->flags && d->f_in && d->f_out, fn, "flags, f_in, f_out required");
     JRL_REQUIRE(d->f_in != d->f_out, fn, "f_out must not alias f_in (double-buffered pull scheme)");
     JRL_REQUIRE(dims_ok(d->B, d->H, d->W) && d->H >= 3 && d->W >= 3, fn, "B >= 1, H >= 3, W >= 3 required");
-    JRL_REQUIRE(d->op >= 0 && d->op <= 2, fn, "unknown operator");
+    JRL_REQUIRE(d->op >= 0 && d->op <= 3, fn, "unknown operator");
+    JRL_REQUIRE(d->op != JRL_OP_NONE || d->force_vec != 8, fn, "JRL_OP_NONE has no pipelined variant");
+    JRL_REQUIRE(d->op != JRL_OP_NONE || (!d->is_convection && d->rho_out && d->vel_out), fn,
+                "JRL_OP_NONE (no collision) is the fluid form's first half: rho_out and vel_out required");
     JRL_REQUIRE(d->op != JRL_OP_MRT || d->mrt, fn, "MRT needs the 9x9 matrix");
     JRL_REQUIRE(!(d->is_convection && d->op != JRL_OP_BGK), fn, "convection is BGK only");
     JRL_REQUIRE(d->op != JRL_OP_KBC || d->kbc_type == JRL_KBC_LBGK || d->kbc_type == JRL_KBC_A || d->kbc_type == JRL_KBC_B ||
                     d->kbc_type == JRL_KBC_C || d->kbc_type == JRL_KBC_D,
                 fn, "Please specific a right KBC Type value");
     JRL_REQUIRE(d->axisym >= 0 && d->axisym <= 2, fn, "axisym must be 0, 1 or 2");
-    JRL_REQUIRE(d->axisym == 0 || d->is_convection, fn,
+    JRL_REQUIRE(d->axisym == 0 || d->is_convection || d->op == JRL_OP_NONE, fn,
                 "the axisymmetric FLUID source needs neighbours' post-stream moments: use the two-launch path");
     JRL_REQUIRE(!(d->is_convection && d->axisym != 0) || d->mesh_grid, fn, "axisymmetric concentration step needs mesh_grid");
     JRL_REQUIRE(!d->is_convection || d->vel, fn, "concentration step needs the advecting velocity in `vel`");

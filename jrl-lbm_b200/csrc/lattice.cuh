@@ -25,7 +25,7 @@ enum : uint8_t { CT_NOTHING = 0, CT_FLUID = 1, CT_OBSTACLE = 2, CT_EMPTY = 4, CT
 enum : int { AXI_NOT = 0, AXI_X = 1, AXI_Y = 2 };
 // utils/types.py:18-23
 enum : int { KBC_LBGK = 0, KBC_A = 0x85, KBC_B = 0x86, KBC_C = 0x89, KBC_D = 0x8A };
-enum : int { OP_BGK = 0, OP_MRT = 1, OP_KBC = 2 };
+enum : int { OP_BGK = 0, OP_MRT = 1, OP_KBC = 2, OP_NONE = 3 };
 // Template values OP_KBC_T0 + i select KBC with the variant known at compile time (i: 0 LBGK, 1 A, 2 B, 3 C, 4 D), which
 // removes the run-time select chains and the dead central-moment code of the other variants from the hot kernels
 // (~100 instructions per cell of ~940); OP_KBC itself keeps the run-time dispatch on p.kbc_type.
@@ -574,6 +574,8 @@ __device__ __forceinline__ void collide_cell(const CollideParams &p, float rho, 
                                              const float *G, float f[9])
 {
     const int op = OP < 0 ? p.op : (OP >= OP_KBC_T0 ? (int)OP_KBC : OP);
+    if (op == OP_NONE)
+        return;  // streaming + boundaries + moments only (first half of the two-launch axisymmetric fluid step)
     const float ux_raw = ux, uy_raw = uy;  // the KBC moments use the unshifted velocity (LBM_collision_KBC_2d.py:295-305)
     if (has_force)
         half_force_shift(rho, ux, uy, fx, fy);

@@ -24,7 +24,7 @@ _lib = None
 
 AXI_NOT, AXI_X, AXI_Y = 0, 1, 2
 TIP_BOX, TIP_CONE45 = 0, 1
-OP_BGK, OP_MRT, OP_KBC = 0, 1, 2
+OP_BGK, OP_MRT, OP_KBC, OP_NONE = 0, 1, 2, 3
 SUM_SLOTS = 64
 
 

@@ -24,6 +24,7 @@ import jrl_lazy as L
 import jrl_native as N
 from jrl_lazy import resolve
 
+_TWO_LAUNCHES = "axisymmetric fluid source needs the neighbours' post-stream moments: fused first half + collision"
 CELL_OBSTACLE = 2
 CELL_INFLOW_2 = 32
 _KBC_CODES = (0, 0x85, 0x86, 0x89, 0x8A)
@@ -387,7 +388,13 @@ class LBMCollision2d:
             why = self._fusable(P, dx, dt, f, rho, vel, flags, mesh_grid, is_convection, tau)
             if why is None:
                 return self._fused_step(P, dx, dt, op, kbc, tau, force, mesh_grid, is_convection)
-            L._why(why)
+            if why is _TWO_LAUNCHES:
+                # axisymmetric FLUID form (JRL stage A): its source term takes gradients of the NEW moments, so the
+                # step is two launches -- streaming + wall + moments fused (JRL_OP_NONE), then this collision
+                f = self._fused_step(P, dx, dt, N.OP_NONE, 0, tau, None, None, False)
+                rho, vel = P.real["rho"], P.real["vel"]
+            else:
+                L._why(why)
         f, rho, vel, flags, force, mesh_grid = (resolve(t) for t in (f, rho, vel, flags, force, mesh_grid))
         B, H, W = _dims(f)
         force = _full(force, (B, 2, H, W), "force", f)
@@ -428,8 +435,6 @@ class LBMCollision2d:
         else:
             if m["kind"] != "fluid" or not P.owns(rho, "rho") or not P.owns(vel, "vel"):
                 return "collision without this step's macro_compute result"
-            if self.axisymmetric_type != N.AXI_NOT:
-                return "axisymmetric fluid source needs post-stream moments of the neighbours (two passes)"
             if (P.rho_in is None or P.vel_in is None) and self._has_inflow(P.flags):
                 return "INFLOW cells with rho / vel not given to propagation()"
             if m["obj"]._contact_angle is not None and (H < 4 or W < 4):
@@ -442,6 +447,8 @@ class LBMCollision2d:
                 return "moving wall and macro_compute were given different previous velocities"
         if self.axisymmetric_type != P.prop.axisymmetric_type or self.axisymmetric_type != m["obj"].axisymmetric_type:
             return "solver objects disagree on the symmetry axis"
+        if not is_convection and self.axisymmetric_type != N.AXI_NOT:
+            return _TWO_LAUNCHES
         return None
 
     def _has_inflow(self, flags):
@@ -461,7 +468,7 @@ class LBMCollision2d:
         fs = cache.get(key)
         if fs is None:
             par = SimpleNamespace(tau=tau, axisymmetric_type=self.axisymmetric_type, contact_angle=ca, device=P.f_in.device)
-            name = {N.OP_BGK: "bgk", N.OP_MRT: "mrt", N.OP_KBC: "kbc"}[op]
+            name = {N.OP_BGK: "bgk", N.OP_MRT: "mrt", N.OP_KBC: "kbc", N.OP_NONE: "none"}[op]
             fs = jrl_step.FusedStep(par, operator=name, kbc_type=kbc if op == N.OP_KBC else None, tau=tau,
                                     tau_D=tau if is_convection else None, is_convection=is_convection, dx=dx, dt=dt,
                                     contact_angle=ca, mrt=self._mrt if op == N.OP_MRT else None)

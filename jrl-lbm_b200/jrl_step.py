@@ -19,14 +19,15 @@ import torch
 import jrl_native as N
 from jrl_solver import _KBC_CODES, _dims, _full, mrt_operator
 
-_OPS = {"bgk": N.OP_BGK, "mrt": N.OP_MRT, "kbc": N.OP_KBC}
+_OPS = {"bgk": N.OP_BGK, "mrt": N.OP_MRT, "kbc": N.OP_KBC, "none": N.OP_NONE}
 
 
 class FusedStep:
     """Configured once per run (operator, tau, symmetry, contact angle); `step()` per time step.
 
     parameters : SimulationParameters (tau, axisymmetric_type, contact_angle are read)
-    operator   : 'bgk' | 'mrt' | 'kbc'
+    operator   : 'bgk' | 'mrt' | 'kbc' | 'none' (streaming + boundaries + moments, no collision: the first half of the
+                 axisymmetric fluid step, whose collision needs the neighbours' new moments and is a second launch)
     is_convection : advection-diffusion form for the concentration field (BGK, relaxation tau_D)
     """
 
@@ -294,7 +295,7 @@ def fluid_walk(collision, f, flags, rho, vel, mesh_grid, force, walks, nsteps, *
     w.vel[0] = N.tensor_ptr(vel, "vel", shape=(1, 2, H, W), like=f).value
     w.vel[1] = vel2.data_ptr()
     N.call("jrl_fluid_walk_f32", ctypes.byref(w), int(nsteps), like=f)
-    N.launch_count += max(0, 5 * int(nsteps) - 1)
+    N.launch_count += max(0, 3 * int(nsteps) - 1)
     try:
         torch.autograd.graph.increment_version(flags)
     except AttributeError:

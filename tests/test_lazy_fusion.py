@@ -70,16 +70,27 @@ def _stage_a(api, dev):
     kw = dict(res=(48, 32), steps=15, vel_obs=0.02, gravity_strength=2e-5, **JRL)
     L.ENABLED = False
     try:
+        n0 = jrl_native.launch_count
         a = S.jrl_fluid(api, dev, **kw)
+        n_eager = jrl_native.launch_count - n0
     finally:
         L.ENABLED = True
+    n0 = jrl_native.launch_count
     b = S.jrl_fluid(api, dev, **kw)
+    n_lazy = jrl_native.launch_count - n0
     _identical(a, b)
+    assert n_eager - n_lazy == 2 * 15, (n_eager, n_lazy)   # 4 launches per step -> 2
 
 
-def test_stage_a_replays_eagerly_emu(emu_api):
-    """The axisymmetric fluid collision is not a single pass: the recorded calls run one launch each, same bits."""
+def test_stage_a_is_two_launches_emu(emu_api):
+    """The axisymmetric fluid collision needs the neighbours' new moments: streaming + wall + moments fuse into one
+    launch (JRL_OP_NONE), the collision is the second; same bits as the four launches."""
     _stage_a(emu_api, torch.device("cpu"))
+
+
+@pytest.mark.gpu
+def test_stage_a_is_two_launches_gpu(cuda_api):
+    _stage_a(cuda_api, torch.device("cuda:0"))
 
 
 def _touch(api, dev):
