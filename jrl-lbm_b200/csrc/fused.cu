@@ -1276,7 +1276,68 @@ extern "C" int jrl_run_f32(const jrl_step_desc *d0, int nsteps, int store_every,
     const bool pp_rho = d.rho != nullptr && d.rho_out != nullptr;
     const bool pp_vel = !d.is_convection && d.vel != nullptr && d.vel_out != nullptr;
     float *const rho_last = d.rho_out, *const vel_last = d.vel_out;
-    for (int i = 0; i < nsteps; ++i)
+    int first = 0;
+#ifndef JRL_HOST_EMU
+    // Small grids are paced by the host's launch rate (2.6 us per cudaLaunchKernelEx at 130^2, where the kernel itself
+    // takes ~1.5 us): replay the loop from a CUDA graph.  The step sequence has period 2 (ping-pong buffers), so
+    // kGraphSteps (even) steps are captured once on a private stream and the executable graph is launched on the
+    // caller's stream as many times as it fits; the remainder -- at least the last step, which stores the moments --
+    // runs as plain launches.  Any failure of the capture machinery falls back to plain launches for everything.
+    constexpr int kGraphSteps = 256;
+    const bool periodic = (pp_rho || pp_vel || store_every == 0) && (d.sums == nullptr || sums_stride == 0);
+    if (periodic && nsteps >= 4 * kGraphSteps && (long long)d.B * d.H * d.W <= (1ll << 19) && d.slab_rows == 0)
+    {
+        cudaStream_t cs = nullptr;
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        int launched = 0;
+        bool ok = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+        if (ok)
+        {
+            jrl_step_desc c = d;
+            for (int i = 0; i < kGraphSteps && ok; ++i)
+            {
+                if (!pp_rho && !pp_vel)
+                    c.rho_out = nullptr, c.vel_out = nullptr;
+                ok = step_once(&c, cs) == 0;
+                const float *fi = c.f_in;
+                c.f_in = c.f_out;
+                c.f_out = const_cast<float *>(fi);
+                if (pp_rho)
+                    std::swap(c.rho, c.rho_out);
+                if (pp_vel)
+                    std::swap(c.vel, c.vel_out);
+            }
+            ok = (cudaStreamEndCapture(cs, &graph) == cudaSuccess) && ok && graph != nullptr;
+        }
+        if (ok)
+            ok = cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess;
+        if (ok)
+        {
+            const int reps = (nsteps - 1) / kGraphSteps;  // leaves 1 .. kGraphSteps steps for the plain loop
+            for (int r = 0; r < reps && ok; ++r)
+            {
+                ok = cudaGraphLaunch(exec, (cudaStream_t)stream) == cudaSuccess;
+                launched += ok ? 1 : 0;
+            }
+            if (ok)
+                first = reps * kGraphSteps;  // an even count: the buffers are back in their starting roles
+        }
+        if (exec)
+            cudaGraphExecDestroy(exec);
+        if (graph)
+            cudaGraphDestroy(graph);
+        if (cs)
+            cudaStreamDestroy(cs);
+        if (!ok)
+        {
+            cudaGetLastError();  // clear the error; fall back to plain launches unless part of the run is already enqueued
+            JRL_REQUIRE(launched == 0, fn, "CUDA graph replay failed after some of its launches");
+        }
+    }
+#endif
+    for (int i = first; i < nsteps; ++i)
     {
         if (!pp_rho && !pp_vel)
         {
