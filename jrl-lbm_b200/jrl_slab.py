@@ -16,9 +16,11 @@ The exchange moves 2 x 9 x W fp32 per rank per step (2.4 MB at W = 32768) agains
 A slab step is ~10 stream operations (three step launches with their work-list passes, pack / NCCL send-recv /
 unpack) issued from Python: ~150 us of host time, which the 1.7 ms interior of the 32768^2 grid hides but the 170 us
 step of the 8192^2 concentration grid on 8 GPUs does not (66 % strong-scaling efficiency in round 1).  `step()`
-therefore captures the whole step -- both streams and the NCCL point-to-point calls -- into a CUDA graph per
-ping-pong parity once the same call has been seen twice, and replays it: one graph launch per step
-(JRL_SLAB_GRAPH=0 disables this).
+can therefore capture the whole step -- both streams and the NCCL point-to-point calls -- into a CUDA graph per
+ping-pong parity once the same call has been seen twice, and replay it: one graph launch per step.
+EXPERIMENTAL and OFF by default (JRL_SLAB_GRAPH=1 enables it): the one 2-GPU run made with it on did not finish
+inside its time limit and there was no GPU budget left to find out why; the eager path is the one the parity checks
+(tools/check_slab_nccl.py) and the scaling numbers were taken on.
 """
 from __future__ import annotations
 
@@ -59,7 +61,7 @@ class SlabLattice:
         self.f = None       # current populations  [B,9,nrows+2,W]
         self.f_next = None  # double buffer
         self.fields = {}    # name -> slab tensor of the static / per-step inputs (flags, phi_obs, vel, ...)
-        self.use_graph = self.cuda and os.environ.get("JRL_SLAB_GRAPH", "1") != "0"
+        self.use_graph = self.cuda and os.environ.get("JRL_SLAB_GRAPH", "0") == "1"
         self._graphs = {}   # call signature -> [times seen eagerly, CUDAGraph or None]
         self.graph_replays = 0
 
