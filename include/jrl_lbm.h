@@ -208,6 +208,22 @@ typedef struct jrl_step_desc
 } jrl_step_desc;
 int jrl_step_f32(const jrl_step_desc *d, void *stream);
 
+/* jrl_step_f32 without any allocation anywhere.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same descriptor, same results, but `tile_mask` and `worklist` must be NULL: the scratch the
+ * pipelined kernel needs (packed tile mask + boundary-group work list) lives in a file-scope `static __device__`
+ * array of JRL_NOALLOC_SCRATCH_BYTES (4 MiB) that every GPU loading the library holds until exit; the tile mask is
+ * rebuilt from `flags` by every call.  LIMIT: jrl_tile_mask_bytes() rounded up to 256 + jrl_worklist_bytes() must fit
+ * in the 4 MiB (grids up to about 4096 x 4096 cells per call); larger grids are rejected with JRL_ERR_ARG and a
+ * message -- use jrl_step_f32 with caller-provided scratch there.  The call issues no cudaMalloc / cudaFree and no
+ * allocating library routine (kernel launches and one 4-byte cudaMemsetAsync only).  All calls on a device SHARE the
+ * array, which keeps the last call's contents (everything that must start at zero is cleared by the call itself):
+ * two calls that overlap on the GPU (different streams) race; calls on one stream are safe.
+ * jrl_step_noalloc_max_bytes() returns JRL_NOALLOC_SCRATCH_BYTES. */
+#define JRL_NOALLOC_SCRATCH_BYTES (4ll << 20)
+int jrl_step_noalloc_f32(const jrl_step_desc *d, void *stream);
+long long jrl_step_noalloc_max_bytes(void);
+
 /* Multi-step driver: `nsteps` lattice updates with the descriptor's buffers used as ping-pong pairs --
  * the time loop of the reference's demos (demo_2d_LBM.py:101-119, demo_2d_LBM_cylinder.py:138-172)
  * below the ABI, for grids small enough to be paced by the host.  Step i reads (f_in, rho, vel) and writes

@@ -1262,6 +1262,82 @@ static int step_once(const jrl_step_desc *d, void *stream)
 
 extern "C" int jrl_step_f32(const jrl_step_desc *d, void *stream) { return step_once(d, stream); }
 
+// ---- allocation-free variant of the pipelined step (no counterpart in the reference)
+//      -----------------------------------------------------------------------------------------
+// The pipelined kernel needs two pieces of scratch: the packed tile mask and the work list through which it defers
+// its boundary groups (jrl_step_desc.tile_mask / .worklist, normally device buffers the caller allocates).  Callers
+// that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) use this entry point,
+// whose scratch is the file-scope array below: JRL_NOALLOC_SCRATCH_BYTES per GPU that loads the library, held until
+// exit, SHARED by every call on that device (calls that overlap on the GPU race; the array keeps the last call's
+// contents: the mask is fully rewritten and the work-list counter cleared by every call).
+constexpr long long kNoAllocScratchBytes = JRL_NOALLOC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// Device address of g_noalloc_scratch on the current device.  In host code the array's NAME is only a host-side
+// stand-in for the symbol, not a device address: it must go through cudaGetSymbolAddress, once per device, with that
+// device current.
+static int noalloc_scratch(unsigned char **out)
+{
+#ifdef JRL_HOST_EMU
+    *out = g_noalloc_scratch;
+    return JRL_OK;
+#else
+    static unsigned char *ptrs[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess)
+        return JRL_ERR_CUDA;
+    if (dev < 0 || dev >= 64)
+        return fail_arg("jrl_step_noalloc_f32", "device ordinal beyond 63");
+    if (ptrs[dev] == nullptr)
+    {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr)
+        {
+            cudaGetLastError();
+            return fail_arg("jrl_step_noalloc_f32", "cudaGetSymbolAddress(g_noalloc_scratch) failed");
+        }
+        ptrs[dev] = static_cast<unsigned char *>(p);
+    }
+    *out = ptrs[dev];
+    return JRL_OK;
+#endif
+}
+
+extern "C" long long jrl_step_noalloc_max_bytes(void) { return kNoAllocScratchBytes; }
+
+extern "C" int jrl_step_noalloc_f32(const jrl_step_desc *d0, void *stream)
+{
+    const char *fn = "jrl_step_noalloc_f32";
+    JRL_REQUIRE(d0, fn, "null descriptor");
+    JRL_REQUIRE(d0->tile_mask == nullptr && d0->worklist == nullptr, fn,
+                "tile_mask and worklist must be NULL: this entry point supplies them from its static scratch");
+    JRL_REQUIRE(dims_ok(d0->B, d0->H, d0->W), fn, "B >= 1, H, W >= 2 required");
+    const int Hs = d0->slab_rows > 0 ? d0->slab_rows + 2 : d0->H;
+    // scratch layout: [0, mask_bytes) tile mask, then (256-byte aligned) the work list of jrl_worklist_bytes()
+    const long long mask_bytes = ((long long)jrl_tile_mask_bytes(d0->B, Hs, d0->W) + 255) / 256 * 256;
+    const long long wl_bytes = jrl_worklist_bytes(d0->B, Hs, d0->W);
+    JRL_REQUIRE(mask_bytes > 0 && wl_bytes > 0 && mask_bytes + wl_bytes <= kNoAllocScratchBytes, fn,
+                "grid too large for the static scratch (tile mask + work list exceed JRL_NOALLOC_SCRATCH_BYTES = 4 MiB, "
+                "about 4096 x 4096 cells): use jrl_step_f32 with caller-provided scratch");
+    jrl_step_desc d = *d0;
+    const bool masked = d.flags != nullptr && d.W % 16 == 0 && d.W >= JRL_PIPE_CW && (uintptr_t)d.flags % 16 == 0;
+    if (masked)  // otherwise the step takes the register kernel, which uses no scratch
+    {
+        unsigned char *base = nullptr;
+        const int rc = noalloc_scratch(&base);
+        if (rc != JRL_OK)
+            return rc;
+        const int mrc = jrl_tile_mask_u8(d.flags, base, d.B, Hs, d.W, stream);
+        if (mrc != JRL_OK)
+            return mrc;
+        d.tile_mask = base;
+        d.worklist = base + mask_bytes;
+        d.worklist_bytes = wl_bytes;
+    }
+    return step_once(&d, stream);
+}
+
 // Multi-step driver: the time loop of the reference's demos (demo_2d_LBM.py:101-119 and siblings) moved
 // below the C ABI, so that small, launch-bound grids are not paced by the Python interpreter.
 extern "C" int jrl_run_f32(const jrl_step_desc *d0, int nsteps, int store_every, long long sums_stride, void *stream)

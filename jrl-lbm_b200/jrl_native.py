@@ -93,6 +93,8 @@ PROTOTYPES = {
     "jrl_strip_flux_f32": [_vp, _vp, _i, _i, _vp, _i, _i, _vp],
     "jrl_momentum_exchange_f32": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "jrl_step_f32": [POINTER(StepDesc), _vp],
+    "jrl_step_noalloc_f32": [POINTER(StepDesc), _vp],
+    "jrl_step_noalloc_max_bytes": [],
     "jrl_run_f32": [POINTER(StepDesc), _i, _i, ctypes.c_longlong, _vp],
     "jrl_tile_mask_bytes": [_i, _i, _i],
     "jrl_worklist_bytes": [_i, _i, _i],
@@ -110,7 +112,7 @@ def _bind(lib):
     for name, argtypes in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the library lacks a declared symbol
         fn.argtypes = argtypes
-        fn.restype = c_char_p if name == "jrl_last_error" else (ctypes.c_longlong if name == "jrl_worklist_bytes" else c_int)
+        fn.restype = c_char_p if name == "jrl_last_error" else (ctypes.c_longlong if name in ("jrl_worklist_bytes", "jrl_step_noalloc_max_bytes") else c_int)
     return lib
 
 

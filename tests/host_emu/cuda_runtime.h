@@ -19,6 +19,7 @@ static inline float __int_as_float(int i) { float x; std::memcpy(&x, &i, 4); ret
 #define __forceinline__ inline __attribute__((always_inline))
 #define __launch_bounds__(...)
 #define __grid_constant__
+#define __align__(n) __attribute__((aligned(n)))
 
 struct uint3
 {
