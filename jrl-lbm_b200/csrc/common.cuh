@@ -77,9 +77,21 @@ __device__ __forceinline__ void pdl_enter()
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
+// Set while jrl_run_f32 captures its step sequence into a CUDA graph: the captured launches are plain (fully
+// serialised) kernel nodes, without the programmatic-serialisation attribute.
+inline bool &pdl_disabled()
+{
+    static bool off = false;
+    return off;
+}
 template <typename... KArgs, typename... Args>
 inline void launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t stream, Args &&...args)
 {
+    if (pdl_disabled())
+    {
+        kern<<<grid, block, 0, stream>>>(KArgs(args)...);
+        return;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;

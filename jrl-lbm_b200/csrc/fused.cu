@@ -1360,7 +1360,9 @@ extern "C" int jrl_run_f32(const jrl_step_desc *d0, int nsteps, int store_every,
     // caller's stream as many times as it fits; the remainder -- at least the last step, which stores the moments --
     // runs as plain launches.  Any failure of the capture machinery falls back to plain launches for everything.
     constexpr int kGraphSteps = 256;
-    const bool periodic = (pp_rho || pp_vel || store_every == 0) && (d.sums == nullptr || sums_stride == 0);
+    const char *genv = getenv("JRL_RUN_GRAPH");  // 0: never replay; 1: captured launches keep PDL; default 2: plain nodes
+    const int gmode = genv ? atoi(genv) : 2;
+    const bool periodic = gmode != 0 && (pp_rho || pp_vel || store_every == 0) && (d.sums == nullptr || sums_stride == 0);
     if (periodic && nsteps >= 4 * kGraphSteps && (long long)d.B * d.H * d.W <= (1ll << 19) && d.slab_rows == 0)
     {
         cudaStream_t cs = nullptr;
@@ -1372,6 +1374,7 @@ extern "C" int jrl_run_f32(const jrl_step_desc *d0, int nsteps, int store_every,
         if (ok)
         {
             jrl_step_desc c = d;
+            pdl_disabled() = gmode != 1;
             for (int i = 0; i < kGraphSteps && ok; ++i)
             {
                 if (!pp_rho && !pp_vel)
@@ -1385,6 +1388,7 @@ extern "C" int jrl_run_f32(const jrl_step_desc *d0, int nsteps, int store_every,
                 if (pp_vel)
                     std::swap(c.vel, c.vel_out);
             }
+            pdl_disabled() = false;
             ok = (cudaStreamEndCapture(cs, &graph) == cudaSuccess) && ok && graph != nullptr;
         }
         if (ok)
