@@ -578,14 +578,14 @@ def main():
     peak, peak_src = measured_peak()
     traffic = None
     try:  # DRAM bytes per lattice update of the dominant kernel from the committed ncu capture, scaled to this launch
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as fh:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as fh:
             traffic = float(json.load(fh)["dram_bytes_per_lup"]) * G * G / world
     except Exception:
         pass
     achieved = BYTES_PER_LUP * G * G / world / (ms_per_step * 1e-3) / 1e9   # per GPU: its cells / the step time
     roofline = {"bound": "hbm", "kernel": "jrl::pipe::k_step_pipe<OP_BGK, 0, 4, 2, 2> (jrl_step_f32; 512-cell tiles, TMA ring, producer warp)", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": traffic,
-                "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per lattice update at 8192^2 (profiles/r1_traffic.json) x cells of this launch",
+                "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per lattice update at 8192^2 (profiles/r2_traffic.json) x cells of this launch",
                 "algorithmic_bytes_per_launch": BYTES_PER_LUP * G * G / world,
                 "note": "per GPU; 72 B per lattice update x cells per rank / CUDA-event step time (1 dominant launch per step)"}
     line = {"metric": METRIC, "value": mlups, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
