@@ -62,6 +62,7 @@ class SlabLattice:
         self.f_next = None  # double buffer
         self.fields = {}    # name -> slab tensor of the static / per-step inputs (flags, phi_obs, vel, ...)
         self.use_graph = self.cuda and os.environ.get("JRL_SLAB_GRAPH", "0") == "1"
+        self._descs = {}    # (parity, argument set) -> the three cached jrl_step_desc of a step
         self._graphs = {}   # call signature -> [times seen eagerly, CUDAGraph or None]
         self.graph_replays = 0
 
@@ -196,19 +197,40 @@ class SlabLattice:
                 args["rho_out"] = self._moment_buffer("rho_out", 1)
             if "vel_out" not in args and not fs.is_convection:
                 args["vel_out"] = self._moment_buffer("vel_out", 2)
-        common = dict(f_out=self.f_next, slab=(r0, n, self.H), store_moments=store, **args)
+        # The three step descriptors (two edge rows, interior) are built once per ping-pong parity and argument set
+        # and reused: building one costs ~40 us of Python (pointer validation), which at 8 GPUs is as long as the
+        # interior kernel of the 8192^2 concentration grid.  The edge rows take the register kernel (force_vec = 4:
+        # ONE launch each; the pipelined kernel would add its tile-mask, memset and work-list launches for a single row).
+        key = (self.f.data_ptr(), flags.data_ptr(), flags._version, store,
+               tuple(sorted((k, (v.data_ptr(), v._version) if isinstance(v, torch.Tensor) else v) for k, v in args.items())),
+               None if rho is None else rho.data_ptr(), None if vel is None else vel.data_ptr())
+        descs = self._descs.get(key)
+        if descs is None:
+            if len(self._descs) > 8:
+                self._descs.clear()
+            fv_edge = 4 if (self.W % 4 == 0 and self.W >= 8) else 0
+            descs = []
+            for rows, fv in (((r0, r0 + 1), fv_edge), ((r0 + n - 1, r0 + n), fv_edge), ((r0 + 1, r0 + n - 1), 0)):
+                d, _, _, _, keep = fs._desc(self.f, flags, rho, vel, self.f_next, args.get("rho_out"), args.get("vel_out"), store,
+                                            args.get("phi_obs"), args.get("force"), args.get("mesh_grid"), args.get("inflow_vel"),
+                                            args.get("inflow_density"), args.get("use_wall", False), args.get("obs_vel"),
+                                            args.get("wall_phi"), args.get("clamp01", False), (r0, n, self.H), rows, fv,
+                                            args.get("sums"))
+                descs.append((d, keep))
+            self._descs[key] = descs
+        like = self.f
         # 1. edge rows first: they are what the neighbours wait for
-        fs.step(self.f, flags, rho, vel, rows=(r0, r0 + 1), **common)
-        fs.step(self.f, flags, rho, vel, rows=(r0 + n - 1, r0 + n), **common)
+        N.call("jrl_step_f32", ctypes.byref(descs[0][0]), like=like)
+        N.call("jrl_step_f32", ctypes.byref(descs[1][0]), like=like)
         if self.overlap:
             main = torch.cuda.current_stream(self.device)
             self.comm_stream.wait_stream(main)
             with torch.cuda.stream(self.comm_stream):
                 self.exchange(self.f_next)
-            fs.step(self.f, flags, rho, vel, rows=(r0 + 1, r0 + n - 1), **common)  # 2. interior overlaps the exchange
+            N.call("jrl_step_f32", ctypes.byref(descs[2][0]), like=like)  # 2. interior overlaps the exchange
             main.wait_stream(self.comm_stream)
         else:
-            fs.step(self.f, flags, rho, vel, rows=(r0 + 1, r0 + n - 1), **common)
+            N.call("jrl_step_f32", ctypes.byref(descs[2][0]), like=like)
             self.exchange(self.f_next)
         self.f, self.f_next = self.f_next, self.f
         return self.f
