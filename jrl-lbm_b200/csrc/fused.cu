@@ -677,6 +677,59 @@ __device__ __forceinline__ void issue_tile(const StepArgs &a, const Tile &tl, St
     }
 }
 
+// All-OBSTACLE group away from the domain edges (see the consumer loop): store the reflected populations and carry the
+// moments over, exactly as step_finish() does for OBSTACLE cells (old rho / u / C kept; concentration clamp applied;
+// interior solid cells get rho = 0 under the contact-angle option, LBM_macro_compute_2d.py:237-271).
+template <int VEC>
+struct SolidPops
+{
+    float v[VEC][9];
+};
+template <int VEC, int CONV>
+__device__ __noinline__ void solid_group_store(const StepArgs &a, int b, int y, int x0, const SolidPops<VEC> sp)
+{
+    const Grid &g = a.g;
+    const long long r0 = cell(g, y, y, 0);
+    const float *rho = a.rho ? a.rho + b * g.HW : nullptr;
+    const float *vel = a.vel ? a.vel + b * 2 * g.HW : nullptr;
+    float *fo = a.f_out + (long long)b * 9 * g.HW + r0 + x0;
+#pragma unroll
+    for (int q = 0; q < 9; ++q)
+    {
+        float v[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k)
+            v[k] = sp.v[k][q];
+        VecIO<VEC>::store(fo + q * g.HW, v);
+    }
+    float r[VEC], ux[VEC], uy[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k)
+    {
+        const long long self = r0 + x0 + k;
+        r[k] = rho ? rho[self] : 0.f;
+        if (CONV != 0)
+        {
+            if (a.clamp01)
+                r[k] = fminf(fmaxf(r[k], 0.f), 1.f);
+        }
+        else
+        {
+            ux[k] = vel ? vel[self] : 0.f;
+            uy[k] = vel ? vel[g.HW + self] : 0.f;
+            if (a.use_contact)
+                r[k] = 0.f;  // interior by construction (1 <= y <= H - 2, 1 <= x <= W - 2)
+        }
+    }
+    if (a.rho_out)
+        VecIO<VEC>::store(a.rho_out + b * g.HW + r0 + x0, r);
+    if (CONV == 0 && a.vel_out)
+    {
+        VecIO<VEC>::store(a.vel_out + b * 2 * g.HW + r0 + x0, ux);
+        VecIO<VEC>::store(a.vel_out + b * 2 * g.HW + g.HW + r0 + x0, uy);
+    }
+}
+
 // The rare path of the pipelined kernel, kept out of line so that its registers (neighbour indices, link
 // rules, wall stencil) do not count against the bulk path: one group of VEC cells by the generic rules,
 // moments, collision and stores included.  Returns {sum rho, sum rho ux, sum rho uy, cells}.
@@ -846,6 +899,27 @@ k_step_pipe(const __grid_constant__ StepArgs a, unsigned total, unsigned tpr, un
                     me[k] = CT_FLUID;
                 step_finish<VEC, OP, CONV>(a, g, tl.b, y, x0, cell(g, y, y, 0), fc, me, true, acc, CONV != 0 ? cur : nullptr);
                 cells = (float)VEC;
+            }
+            else if (w[1] == (VEC == 4 ? 0x02020202u : 0x0202u) && y >= 1 && y <= g.H - 2 && x0 >= 1 && x0 + VEC <= g.W - 1)
+            {
+                // A group whose OWN cells are all OBSTACLE, away from the domain edges: a solid cell stores the
+                // reflected incoming set, out[opp(q)] = f[q] @ upstream(q), whatever its neighbours are
+                // (propagation.cu:111-128; lattice.cuh stream_links), keeps its moments and is not collided -- pure data
+                // movement of exactly the values the bulk path pulls.  Without this the inside of a large body (the probe
+                // tip of the scaled C4 grid: 0.5 M groups) goes to the work list -- and, where the list is full (one slab
+                // of an 8-GPU split holds the whole tip), is walked in place at ~20 us per group.  Kept out of line and
+                // out of the bulk branch: a runtime select inside the bulk loops cost the BGK headline 17 %.
+                SolidPops<VEC> sp;
+#pragma unroll
+                for (int q = 0; q < 9; ++q)
+                {
+                    const int ex = JRL_EX(q);
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k)
+                        sp.v[k][opp(q)] = ex == 0 ? tv[q][k] : (ex > 0 ? (k == 0 ? edge[q] : tv[q][k > 0 ? k - 1 : 0])
+                                                                       : (k == VEC - 1 ? edge[q] : tv[q][k < VEC - 1 ? k + 1 : 0]));
+                }
+                solid_group_store<VEC, CONV>(a, tl.b, y, x0, sp);
             }
             else
             {

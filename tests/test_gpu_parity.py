@@ -96,6 +96,11 @@ def test_pipelined_kernel_equals_register_kernel(cuda_api, dev, op, conv, axisym
     flags = st["flags"].clone()
     flags[:, :, 8:30, 100:W - 100] = 1          # a large all-FLUID region so that the staged (bulk) path runs too
     flags[:, :, 12:26, 0:24] = 1                # ... including groups on the x symmetry axis (column 0)
+    flags[:, :, 9:20, 480:560] = 2              # a solid block (all-OBSTACLE groups: the pipelined kernel's data-movement
+    flags[:, :, 0:3, 600:700] = 2               # fast path), across a tile boundary, and solid cells on the first / last
+    flags[:, :, H - 2:H, 300:420] = 2           # rows and columns, where the mirrored neighbour rule applies (generic path)
+    flags[:, :, 20:30, 0:12] = 2
+    flags[:, :, 20:30, W - 10:W] = 2
     fs = jrl_step.FusedStep(P, operator=op, kbc_type=133 if op == "kbc" else None, is_convection=conv,
                             tau_D=0.8 if conv else None)
     mesh = cuda_api.create_2d_meshgrid_tensor((1, 1, H, W), device=dev) + 0.5
