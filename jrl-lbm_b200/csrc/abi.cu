@@ -17,14 +17,13 @@ void set_error(const char *fmt, ...)
 
 int sm_count()
 {
-    static int n = 0;
-    if (n == 0)
-    {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-            n = 148;
-    }
-    return n;
+    static int n[64] = {};  // per device: a process may drive several GPUs (jrl_native.device_of)
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+        return 148;
+    if (n[dev] == 0 && cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+        n[dev] = 148;
+    return n[dev];
 }
 
 }  // namespace jrl

@@ -1057,7 +1057,16 @@ static int launch(const StepArgs &a, int B, cudaStream_t s)
         return launch_one<OP_BGK, 0>(a, total, tpr, rows, s);
     if (a.cp.op == OP_MRT)  // 2 cells per consumer thread, 3 stages (see the dispatch note in step_once)
         return launch_cfg<OP_MRT, 0, 2, 3, JRL_PIPE_MINB>(a, total, tpr, rows, s);
-    return launch_one<OP_KBC, 0>(a, total, tpr, rows, s);
+    // KBC (force_vec = 8 only; the register kernel is the default): variant as a template value, 2 cells per consumer
+    // thread and 3 stages as for MRT -- the operator is issue-bound (~800 instructions per cell)
+    switch (kbc_index_of(a.cp.kbc_type))
+    {
+    case 1: return launch_cfg<OP_KBC_T0 + 1, 0, 2, 3, JRL_PIPE_MINB>(a, total, tpr, rows, s);
+    case 2: return launch_cfg<OP_KBC_T0 + 2, 0, 2, 3, JRL_PIPE_MINB>(a, total, tpr, rows, s);
+    case 3: return launch_cfg<OP_KBC_T0 + 3, 0, 2, 3, JRL_PIPE_MINB>(a, total, tpr, rows, s);
+    case 4: return launch_cfg<OP_KBC_T0 + 4, 0, 2, 3, JRL_PIPE_MINB>(a, total, tpr, rows, s);
+    default: return launch_cfg<OP_KBC_T0 + 0, 0, 2, 3, JRL_PIPE_MINB>(a, total, tpr, rows, s);
+    }
 #endif
 }
 

@@ -140,22 +140,21 @@ class AsyncSnapshotter:
                             C=C, phi=phi_obs, u=u, v=v)
         snap.flush()
 
-    `submit` records an event on the current stream, makes the copy stream wait for it, enqueues the device->pinned
-    copies there and returns; the writer thread synchronises on the copy's own event and then calls `fn` with a dict of
-    numpy arrays (views of the pinned buffers, valid for the duration of the call).  A slot is reused only after its
-    writer call returned, so at most `depth` snapshots are in flight and `submit` blocks (the host thread only) when
-    the writer falls behind.  The tensors are read on the copy stream: the caller must not overwrite them in place
-    before the copy ran -- `record_stream`-style protection is provided by making the NEXT work on the producing
-    stream wait for the copy event (`guard=True`, default), which costs nothing unless the copy is still running."""
+    `submit` copies the fields device-to-device into per-slot staging buffers on the CURRENT stream (in order with the
+    step loop, HBM speed), records an event, makes the copy stream wait for it, enqueues the staging->pinned copies there
+    and returns; the writer thread synchronises on the copy's own event and then calls `fn` with a dict of numpy views
+    of the pinned buffers.  The producing stream never waits for PCIe or for the disk, and the source tensors may be
+    overwritten as soon as `submit` has returned (the step loop's ping-pong buffers are, two steps later).  `depth`
+    snapshots can be in flight; `submit` blocks the host (not the GPU) when all slots are still being written out."""
 
     def __init__(self, depth=2, device=None, guard=True):
         if not torch.cuda.is_available():
             raise RuntimeError("AsyncSnapshotter needs a CUDA device (no CPU path)")
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.depth = int(depth)
-        self.guard = guard
+        self.guard = guard  # kept for call compatibility; unused since snapshots are staged on the device
         self.stream = torch.cuda.Stream(device=self.device)
-        self._slots = [dict(bufs={}, free=threading.Event()) for _ in range(self.depth)]
+        self._slots = [dict(bufs={}, dev={}, free=threading.Event()) for _ in range(self.depth)]
         for s in self._slots:
             s["free"].set()
         self._next = 0
@@ -180,24 +179,31 @@ class AsyncSnapshotter:
         self._next = (self._next + 1) % self.depth
         slot["free"].wait()
         slot["free"].clear()
+        # Snapshot = a device-to-device copy into this slot's staging buffers ON THE PRODUCING STREAM (HBM speed, in
+        # order with the step loop, so the loop may overwrite its ping-pong buffers right after), then the D2H copy of
+        # the staging buffers on the copy stream.  The producing stream never waits for PCIe or the disk; a slot is
+        # reused only after the writer thread has finished with it (slot["free"]).
         cur = torch.cuda.current_stream(self.device)
+        staged = {}
+        for name, t in tensors.items():
+            t = t.detach()
+            d = slot["dev"].get(name)
+            if d is None or d.shape != t.shape or d.dtype != t.dtype:
+                d = slot["dev"][name] = torch.empty(t.shape, dtype=t.dtype, device=self.device)
+            d.copy_(t, non_blocking=True)
+            staged[name] = d
         ready = torch.cuda.Event()
         ready.record(cur)
         self.stream.wait_event(ready)
         host = {}
         with torch.cuda.stream(self.stream):
-            for name, t in tensors.items():
-                t = t.detach()
-                if not t.is_contiguous():
-                    t = t.contiguous()
-                b = self._pinned(slot, name, t)
-                b.copy_(t, non_blocking=True)
+            for name, d in staged.items():
+                b = self._pinned(slot, name, d)
+                b.copy_(d, non_blocking=True)
                 host[name] = b
-                self.bytes_copied += t.numel() * t.element_size()
+                self.bytes_copied += d.numel() * d.element_size()
             done = torch.cuda.Event()
             done.record(self.stream)
-        if self.guard:
-            cur.wait_event(done)
         self.snapshots += 1
         self._q.put((fn, host, done, slot))
 
