@@ -26,6 +26,7 @@ else.  `JRL_LBM_FUSE=0` in the environment turns the whole mechanism off (every 
 from __future__ import annotations
 
 import os
+import sys
 import weakref
 
 import torch
@@ -160,7 +161,8 @@ class PendingStep:
 
     # -- recording -----------------------------------------------------------------------------------------
     def add_wall(self, obj, dt, dx, tau, rho, vel, phi_obs, obs_vel):
-        self.wall = dict(obj=obj, dt=dt, dx=dx, tau=tau, rho=rho, vel=vel, phi_obs=phi_obs, obs_vel=obs_vel)
+        # `rho` is accepted and ignored by the reference's kernel too; not kept (it may be propagation()'s handle)
+        self.wall = dict(obj=obj, dt=dt, dx=dx, tau=tau, rho=None, vel=vel, phi_obs=phi_obs, obs_vel=obs_vel)
         self.watch(vel, phi_obs, obs_vel)
         return self.handle("f_wall", self.f_in.shape, self.f_in)
 
@@ -218,21 +220,40 @@ class PendingStep:
             return
         raise KeyError(role)
 
+    def _visible_outside(self, role):
+        """The recorded input `role` ('rho_in' / 'vel_in') is still reachable by the caller: its handle is alive and
+        unresolved, or the tensor object has more references than this record's own."""
+        ref = self.handles.get(role)
+        h = ref() if ref is not None else None
+        if h is not None and h._real is None:
+            return True
+        t = getattr(self, role)
+        own = 1                                                          # the attribute
+        own += sum(1 for w in self._watch if w[0] is t)                  # version watch list
+        own += sum(1 for d in (self.moments, self.wall) if d for v in d.values() if v is t)
+        return sys.getrefcount(t) - 2 > own                              # - getrefcount's argument and the local `t`
+
     # -- the fused launch ----------------------------------------------------------------------------------------
     def publish_fused(self, rho_out, vel_out):
         """After jrl_step_f32: the moments handles become the launch's outputs; the streamed / wall-corrected
         populations were never stored (their handles replay eagerly if anyone still looks at them)."""
         self.launched = True
         stats["fused"] += 1
-        # jrl_step_f32 does not write the previous-step rho / vel; if the caller still holds the tensors propagation()
-        # returned for them, give them streaming's in-place writes now (one small launch; the demos rebind both names
-        # before collision(), so for them this never runs)
-        alive = [r for r in ("rho_in", "vel_in") if r in self.handles and self.handles[r]() is not None
-                 and self.handles[r]()._real is None]
+        # jrl_step_f32 does not write the previous-step rho / vel.  If the caller can still see them -- through the
+        # handles propagation() returned for them, or through the ORIGINAL tensor objects (more Python references than
+        # this record itself holds) -- give them streaming's in-place writes now (one small launch).  The demos rebind
+        # both names before collision(), so for them this never runs.  (A view of the original tensor held elsewhere
+        # is not detected: set JRL_LBM_FUSE=0 for code that reads pre-step rho / vel through views after a step.)
+        # streaming writes rho only with an inflow density (INFLOW cells) or at INFLOW_2 cells (rho = 1), and vel only
+        # with an inflow velocity (propagation.cu:300, 320-321, 362)
+        written = {"rho_in": self.inflow_density is not None or self.prop._has_inflow2(self.flags),
+                   "vel_in": self.inflow_vel is not None}
+        alive = [r for r in ("rho_in", "vel_in") if written[r] and getattr(self, r) is not None and self._visible_outside(r)]
         if alive:
             self.prop._inflow_apply(self.flags, self.rho_in if "rho_in" in alive else None,
                                     self.vel_in if "vel_in" in alive else None, self.inflow_vel, self.inflow_density)
-            for r in alive:
+        for r in alive:
+            if r in self.handles:
                 self._publish(r, self.rho_in if r == "rho_in" else self.vel_in)
         if self.moments["kind"] == "C":
             # with the clamp fused in, the unclamped sum was never stored: its handle replays eagerly if touched

@@ -166,3 +166,39 @@ def test_flags_cache_is_per_tensor_object_emu(emu_api):
     fs._masks[id(b)] = fs._masks[id(a)]                                   # what an address-keyed cache would do
     m2 = fs._tile_mask(b, 1, 8, 512)
     assert not torch.equal(m2, torch.ones_like(m2)) or m2 is not m1
+
+
+def _original_tensor_still_mutated(api, dev):
+    """A caller that ignores the tensors propagation() returns and keeps using the ORIGINAL rho / vel objects still
+    sees streaming's in-place writes at INFLOW cells after the fused step (propagation.cu:300, 320-321)."""
+    P = api.SimulationParameters(dim=2, dtype=torch.float32, device=dev, simulation_size=(1, 1, 24, 20), dt=1.0,
+                                 contact_angle=None, Q=9, tau=0.7)
+    R = api.SimulationRunner(parameters=P)
+    prop, macro, col = R.create_propagation(), R.create_macro_compute(), R.create_collision()
+    s = S.random_state((24, 20), 3, dev)
+    outs = []
+    for enabled in (False, True):
+        L.ENABLED = enabled
+        try:
+            rho, vel = s["rho"].clone(), s["vel"].clone()
+            res = prop.propagation(f=s["f"], flags=s["flags"], rho=rho, vel=vel, inflow_density=1.0,
+                                   inflow_vel=torch.tensor([0.01, 0.02], device=dev))
+            f2 = res[2]
+            del res
+            r2, v2 = macro.macro_compute(dx=1.0, dt=1.0, f=f2, rho=rho, vel=vel, flags=s["flags"])
+            f3 = col.collision(dx=1.0, dt=1.0, f=f2, rho=r2, vel=v2, flags=s["flags"])
+            outs.append([t.cpu().numpy().copy() for t in (rho, vel, f3)])
+        finally:
+            L.ENABLED = True
+    for a, b in zip(*outs):
+        assert np.array_equal(a, b, equal_nan=True)
+    assert not np.array_equal(outs[1][0], s["rho"].cpu().numpy())   # the inflow density really was written
+
+
+def test_original_tensor_still_mutated_emu(emu_api):
+    _original_tensor_still_mutated(emu_api, torch.device("cpu"))
+
+
+@pytest.mark.gpu
+def test_original_tensor_still_mutated_gpu(cuda_api):
+    _original_tensor_still_mutated(cuda_api, torch.device("cuda:0"))

@@ -115,5 +115,10 @@ def test_demo_unchanged_gpu(name, cuda_api, workdir):
     n0 = _launches()
     got = D.run_case(name, DEMO_CASES, workdir, cpu=False)
     assert _launches() > n0, "the demo ran without a single libjrl_lbm launch"
+    # the reference's four calls per step reach the fused kernel: ONE library launch per step (+ get_feq_ for the
+    # initial state) for C1-C3 (jrl_lazy.py); stage B one per step, stage A two (fused first half + collision)
+    steps = {"c1_bgk": 1000, "c2_mrt": 1000, "c3_cylinder": 1000}.get(name)
+    if steps is not None:
+        assert _launches() - n0 <= steps + 4, f"{name}: {_launches() - n0} library launches for {steps} steps"
     worst = _compare(name, got, want, cpu=False)
     print(f"{name}: worst rel-L2 {worst[0]:.2e} ({worst[1]}), {_launches() - n0} library launches")
