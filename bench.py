@@ -609,6 +609,8 @@ def main():
             line["cpu_baseline"] = info
         print(json.dumps(line), flush=True)
     if world > 1:
+        import jrl_slab
+        jrl_slab.release_all_graphs()   # captured NCCL operations must be gone before the communicator is
         dist.barrier()
         dist.destroy_process_group()
 

@@ -18,14 +18,16 @@ unpack) issued from Python: ~150 us of host time, which the 1.7 ms interior of t
 step of the 8192^2 concentration grid on 8 GPUs does not (66 % strong-scaling efficiency in round 1).  `step()`
 can therefore capture the whole step -- both streams and the NCCL point-to-point calls -- into a CUDA graph per
 ping-pong parity once the same call has been seen twice, and replay it: one graph launch per step.
-EXPERIMENTAL and OFF by default (JRL_SLAB_GRAPH=1 enables it): the one 2-GPU run made with it on did not finish
-inside its time limit and there was no GPU budget left to find out why; the eager path is the one the parity checks
-(tools/check_slab_nccl.py) and the scaling numbers were taken on.
+OFF by default (JRL_SLAB_GRAPH=1 enables it).  With it on the slab run is bit-exact against the single domain
+(tools/check_slab_nccl.py at N = 2), but the captured graphs hold NCCL operations: `release_all_graphs()` (or
+`SlabLattice.close()`) MUST run before `dist.destroy_process_group()`, which otherwise never returns -- the reason
+the first run made with it did not finish.  The eager path is the one the committed scaling numbers were taken on.
 """
 from __future__ import annotations
 
 import ctypes
 import os
+import weakref
 
 import torch
 import torch.distributed as dist
@@ -39,6 +41,16 @@ def slab_rows(H, world, rank):
     n = base + (1 if rank < rem else 0)
     row0 = rank * base + min(rank, rem)
     return row0, n
+
+
+_LATTICES = weakref.WeakSet()
+
+
+def release_all_graphs():
+    """Drop every captured slab-step graph of this process.  MUST run before `dist.destroy_process_group()`: a CUDA graph
+    that holds captured NCCL operations keeps the communicator busy and the destroy call never returns (seen on 2 x B200)."""
+    for lat in list(_LATTICES):
+        lat.close()
 
 
 class SlabLattice:
@@ -65,6 +77,15 @@ class SlabLattice:
         self._descs = {}    # (parity, argument set) -> the three cached jrl_step_desc of a step
         self._graphs = {}   # call signature -> [times seen eagerly, CUDAGraph or None]
         self.graph_replays = 0
+        _LATTICES.add(self)
+
+    def close(self):
+        """Release the captured graphs (see release_all_graphs) and the cached descriptors."""
+        if self._graphs:
+            if self.cuda:
+                torch.cuda.synchronize(self.device)
+            self._graphs.clear()
+        self._descs.clear()
 
     # -- storage ---------------------------------------------------------------------------------
     def empty(self, C, dtype=torch.float32):
@@ -156,10 +177,11 @@ class SlabLattice:
         if ent is None:
             if len(self._graphs) > 16:   # per-step-varying arguments (e.g. a new sums slice every step): stay eager
                 self._graphs.clear()
-            ent = self._graphs[key] = [0, None]
+            ent = self._graphs[key] = [0, None, 0]
         if ent[1] is not None:
             ent[1].replay()
             self.graph_replays += 1
+            N.launch_count += ent[2]   # the library launches this graph holds (counted while it was captured)
             self.f, self.f_next = self.f_next, self.f
             return self.f
         ent[0] += 1
@@ -169,6 +191,7 @@ class SlabLattice:
         # caching allocator have been warmed by the eager calls)
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize(self.device)
+        n0 = N.launch_count
         try:
             with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 self._step(**kw)
@@ -178,7 +201,7 @@ class SlabLattice:
             torch.cuda.synchronize(self.device)
             self.f, self.f_next = self._f_before_capture
             return self._step(**kw)
-        ent[1] = g
+        ent[1], ent[2] = g, N.launch_count - n0
         # the capture only recorded; run it once for this step's effect (the eager swap already happened in _step)
         g.replay()
         self.graph_replays += 1

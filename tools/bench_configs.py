@@ -199,6 +199,8 @@ def main():
         c4_big(S, api, dev, args.big)
     if world > 1:
         import torch.distributed as dist
+        import jrl_slab
+        jrl_slab.release_all_graphs()
         dist.barrier()
         dist.destroy_process_group()
 

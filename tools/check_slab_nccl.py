@@ -29,6 +29,9 @@ def main():
     ap.add_argument("--steps", type=int, default=12)
     args = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    if os.environ.get("JRL_DEBUG_HANG"):  # print every thread's stack and exit if the check has not finished by then
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["JRL_DEBUG_HANG"]), exit=True)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
@@ -82,6 +85,7 @@ def main():
     if rank == 0:
         print(json.dumps(report), flush=True)
     dist.barrier()
+    jrl_slab.release_all_graphs()
     dist.destroy_process_group()
     sys.exit(1 if bad else 0)
 
