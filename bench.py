@@ -447,12 +447,17 @@ def extra_configs(device, rank, world, barrier, peak, G2=8192, K=20):
     h = R.create_collision().get_feq_(dx=1.0, dt=1.0, rho=C, vel=torch.zeros_like(vel))
     kw = dict(phi_obs=phi, mesh_grid=mesh, inflow_density=0, clamp01=True)
     if world > 1:
-        lat = jrl_slab.SlabLattice(fs, G, G, rank=rank, world=world, device=device)
+        # graph=True: the slab step (both streams, NCCL p2p included) is replayed from a CUDA graph -- at 1024 rows per
+        # rank the step's ~15 host calls take longer than its kernels (profiles/r2_slab_trace.md); released before the
+        # process group is destroyed (jrl_slab.release_all_graphs at the end of main)
+        lat = jrl_slab.SlabLattice(fs, G, G, rank=rank, world=world, device=device, graph=os.environ.get("JRL_SLAB_GRAPH", "1") == "1")
         lat.set_state(h, flags=flags, rho=C, vel=vel, **kw)
         Cout = torch.empty_like(C)
 
         def c4_step():
             lat.step(store_moments=True, rho_out=Cout)
+        for _ in range(6):   # both ping-pong parities seen twice: the graphs are captured before the timed steps
+            c4_step()
     else:
         st = [h, torch.empty_like(h), C, torch.empty_like(C)]
 

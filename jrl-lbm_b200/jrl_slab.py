@@ -7,9 +7,9 @@ ghost rows holding the neighbour ranks' edge rows.  Streaming is a radius-1 sten
 exchange of the post-collision populations' edge rows per step is the only communication; the
 periodic wrap of FLUID cells (propagation.cu:86-87) makes the rank topology a ring.
 
-Per step (CUDA):   main stream : update the two edge rows -> record E
-                   comm stream : wait E, pack edge rows, ncclSend/ncclRecv both neighbours, unpack
-                   main stream : update the interior rows (overlaps the exchange), then wait comm
+Per step (CUDA):   comm stream : wait for main, update the two edge rows (one launch each, one cell per thread), pack them,
+                                 ncclSend / ncclRecv with both neighbours, unpack into the ghost rows
+                   main stream : update the interior rows (side by side with all of the above), then wait for comm
 The exchange moves 2 x 9 x W fp32 per rank per step (2.4 MB at W = 32768) against
 72 B x nrows x W of HBM traffic for the interior, so it hides completely behind the interior.
 
@@ -54,7 +54,7 @@ def release_all_graphs():
 
 
 class SlabLattice:
-    def __init__(self, fused, H, W, rank=None, world=None, device=None, group=None, B=1, overlap=True):
+    def __init__(self, fused, H, W, rank=None, world=None, device=None, group=None, B=1, overlap=True, graph=None):
         self.fs = fused
         self.H, self.W, self.B = int(H), int(W), int(B)
         self.group = group
@@ -73,10 +73,12 @@ class SlabLattice:
         self.f = None       # current populations  [B,9,nrows+2,W]
         self.f_next = None  # double buffer
         self.fields = {}    # name -> slab tensor of the static / per-step inputs (flags, phi_obs, vel, ...)
-        self.use_graph = self.cuda and os.environ.get("JRL_SLAB_GRAPH", "0") == "1"
+        self.use_graph = self.cuda and (os.environ.get("JRL_SLAB_GRAPH", "0") == "1" if graph is None else bool(graph))
         self._descs = {}    # (parity, argument set) -> the three cached jrl_step_desc of a step
         self._graphs = {}   # call signature -> [times seen eagerly, CUDAGraph or None]
         self.graph_replays = 0
+        # host order of the interior launch and the exchange's calls (both orders give the same device-side dependencies)
+        self.interior_first = os.environ.get("JRL_SLAB_ORDER", "interior_first") == "interior_first"
         _LATTICES.add(self)
 
     def close(self):
@@ -222,7 +224,7 @@ class SlabLattice:
                 args["vel_out"] = self._moment_buffer("vel_out", 2)
         # The three step descriptors (two edge rows, interior) are built once per ping-pong parity and argument set
         # and reused: building one costs ~40 us of Python (pointer validation), which at 8 GPUs is as long as the
-        # interior kernel of the 8192^2 concentration grid.  The edge rows take the register kernel (force_vec = 4:
+        # interior kernel of the 8192^2 concentration grid.  The edge rows take the register kernel (force_vec = 1:
         # ONE launch each; the pipelined kernel would add its tile-mask, memset and work-list launches for a single row).
         key = (self.f.data_ptr(), flags.data_ptr(), flags._version, store,
                tuple(sorted((k, (v.data_ptr(), v._version) if isinstance(v, torch.Tensor) else v) for k, v in args.items())),
@@ -231,7 +233,7 @@ class SlabLattice:
         if descs is None:
             if len(self._descs) > 8:
                 self._descs.clear()
-            fv_edge = 4 if (self.W % 4 == 0 and self.W >= 8) else 0
+            fv_edge = 1   # one cell per thread: a one-row launch is latency-bound (32 blocks instead of 8 at W = 8192)
             descs = []
             for rows, fv in (((r0, r0 + 1), fv_edge), ((r0 + n - 1, r0 + n), fv_edge), ((r0 + 1, r0 + n - 1), 0)):
                 d, _, _, _, keep = fs._desc(self.f, flags, rho, vel, self.f_next, args.get("rho_out"), args.get("vel_out"), store,
@@ -242,17 +244,27 @@ class SlabLattice:
                 descs.append((d, keep))
             self._descs[key] = descs
         like = self.f
-        # 1. edge rows first: they are what the neighbours wait for
-        N.call("jrl_step_f32", ctypes.byref(descs[0][0]), like=like)
-        N.call("jrl_step_f32", ctypes.byref(descs[1][0]), like=like)
         if self.overlap:
+            # comm stream (high priority): edge rows -> pack -> NCCL p2p -> unpack; main stream: the interior, which
+            # reads only owned rows of the previous step and writes rows the edge launches do not touch, so the two
+            # run side by side.  (Until round 2 the edge launches sat on the main stream IN FRONT of the interior:
+            # tools/trace_slab.py showed 2 x 40-60 us of one-row kernels serialised with a 185 us interior.)
             main = torch.cuda.current_stream(self.device)
             self.comm_stream.wait_stream(main)
             with torch.cuda.stream(self.comm_stream):
-                self.exchange(self.f_next)
-            N.call("jrl_step_f32", ctypes.byref(descs[2][0]), like=like)  # 2. interior overlaps the exchange
+                N.call("jrl_step_f32", ctypes.byref(descs[0][0]), like=like)
+                N.call("jrl_step_f32", ctypes.byref(descs[1][0]), like=like)
+                if not self.interior_first:
+                    self.exchange(self.f_next)
+            N.call("jrl_step_f32", ctypes.byref(descs[2][0]), like=like)
+            if self.interior_first:
+                with torch.cuda.stream(self.comm_stream):
+                    self.exchange(self.f_next)
             main.wait_stream(self.comm_stream)
         else:
+            # 1. edge rows first: they are what the neighbours wait for
+            N.call("jrl_step_f32", ctypes.byref(descs[0][0]), like=like)
+            N.call("jrl_step_f32", ctypes.byref(descs[1][0]), like=like)
             N.call("jrl_step_f32", ctypes.byref(descs[2][0]), like=like)
             self.exchange(self.f_next)
         self.f, self.f_next = self.f_next, self.f
