@@ -41,6 +41,95 @@ def _problem(api, S, kind):
     return fs, f0, flags, rho, vel, phi
 
 
+def _conc_problem(api):
+    """BASELINE config 4's concentration step (tools/workloads.c4_state: probe tip, x-axis symmetry, INFLOW ring, OUTFLOW
+    edges, interpolated bounce-back, clamp) at 48 x 32; the tip's solid block and its inflow row straddle the slab cuts."""
+    sys.path.insert(0, os.path.join(os.path.dirname(PKG), "tools"))
+    import workloads as WL
+    dev = torch.device("cpu")
+    Hc, Wc = 48, 32
+    P = api.SimulationParameters(simulation_size=(1, 1, Hc, Wc), device=dev, contact_angle=None, axisymmetric_type=1)
+    R = api.SimulationRunner(P)
+    fs = R.create_fused_step(operator="bgk", is_convection=True, tau_D=1.0)
+    flags, mesh, phi, vel, C = WL.c4_state(dev, Hc, Wc, torch.arange(Hc), 1)
+    C = (C * (0.6 + 0.4 * torch.rand(C.shape, generator=torch.Generator().manual_seed(2)))).contiguous()
+    h = R.create_collision().get_feq_(dx=1.0, dt=1.0, rho=C, vel=torch.zeros_like(vel))
+    return fs, h, flags, mesh, phi, vel, C, (Hc, Wc)
+
+
+def _single_conc():
+    S, api = _setup()
+    fs, h, flags, mesh, phi, vel, C, _ = _conc_problem(api)
+    for _ in range(STEPS):
+        h, C = fs.step(h, flags, C, vel, phi_obs=phi, mesh_grid=mesh, inflow_density=0, clamp01=True)
+    return h.numpy(), C.numpy()
+
+
+def _worker_conc(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    S, api = _setup()
+    import jrl_slab
+    fs, h, flags, mesh, phi, vel, C, (Hc, Wc) = _conc_problem(api)
+    lat = jrl_slab.SlabLattice(fs, Hc, Wc, device="cpu")
+    lat.set_state(lat.scatter_global(h), flags=lat.scatter_global(flags), vel=lat.scatter_global(vel),
+                  phi_obs=lat.scatter_global(phi), mesh_grid=lat.scatter_global(mesh), inflow_density=0, clamp01=True)
+    c = lat.scatter_global(C)
+    for _ in range(STEPS):
+        lat.step(rho=c, store_moments=True)
+        c = lat._staging["rho_out"].clone()
+        lat.exchange(c)
+    np.save(os.path.join(out_dir, f"h_{rank}.npy"), lat.owned(lat.f).numpy())
+    np.save(os.path.join(out_dir, f"C_{rank}.npy"), lat.owned(c).numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _wall_problem(api):
+    """BASELINE config 3 (tools/workloads.cylinder_state: MRT, INFLOW / OUTFLOW rows, moving-wall reconstruction around a
+    cylinder) at 48 x 36 with the cylinder centred on a slab cut."""
+    sys.path.insert(0, os.path.join(os.path.dirname(PKG), "tools"))
+    import workloads as WL
+    dev = torch.device("cpu")
+    Hc, Wc = 48, 36
+    flags, phi, rho, vel, inflow_vel = WL.cylinder_state(dev, Hc, Wc, 9, (17.0, 24.5))
+    P = api.SimulationParameters(simulation_size=(1, 1, Hc, Wc), device=dev, tau=0.56, contact_angle=None)
+    R = api.SimulationRunner(P)
+    fs = R.create_fused_step(operator="mrt")
+    f0 = R.create_collision().get_feq_(dx=1.0, dt=1.0, rho=rho, vel=vel)
+    return fs, f0, flags, phi, rho, vel, inflow_vel, (Hc, Wc)
+
+
+def _single_wall():
+    S, api = _setup()
+    fs, f, flags, phi, rho, vel, inflow_vel, _ = _wall_problem(api)
+    zero = torch.zeros_like(vel)
+    for _ in range(STEPS):
+        f, rho, vel = fs.step(f, flags, rho, vel, inflow_density=1.0, inflow_vel=inflow_vel, use_wall=True, wall_phi=phi, obs_vel=zero)
+    return f.numpy(), rho.numpy(), vel.numpy()
+
+
+def _worker_wall(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    S, api = _setup()
+    import jrl_slab
+    fs, f0, flags, phi, rho, vel, inflow_vel, (Hc, Wc) = _wall_problem(api)
+    lat = jrl_slab.SlabLattice(fs, Hc, Wc, device="cpu")
+    lat.set_state(lat.scatter_global(f0), flags=lat.scatter_global(flags), inflow_density=1.0, inflow_vel=inflow_vel,
+                  use_wall=True, wall_phi=lat.scatter_global(phi), obs_vel=lat.scatter_global(torch.zeros_like(vel)))
+    r, v = lat.scatter_global(rho), lat.scatter_global(vel)
+    for _ in range(STEPS):
+        lat.step(rho=r, vel=v, store_moments=True)
+        r, v = lat._staging["rho_out"].clone(), lat._staging["vel_out"].clone()
+        lat.exchange(r)
+        lat.exchange(v)
+    for name, t in (("f", lat.f), ("rho", r), ("vel", v)):
+        np.save(os.path.join(out_dir, f"{name}_{rank}.npy"), lat.owned(t).numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 def _single(kind):
     S, api = _setup()
     fs, f, flags, rho, vel, phi = _problem(api, S, kind)
@@ -84,3 +173,33 @@ def test_slab_equals_single_domain(tmp_path, world, kind):
     got = np.concatenate([np.load(tmp_path / f"slab_{r}.npy") for r in range(world)], axis=2)
     want = _single(kind)
     assert np.array_equal(got, want, equal_nan=True)
+
+
+@pytest.mark.skipif(have_cuda(), reason="CPU/gloo test of the host-side logic")
+@pytest.mark.parametrize("world", [2, 3])
+def test_concentration_slab_equals_single_domain(tmp_path, world):
+    """BASELINE config 4 is "row-slab sharded": the fused concentration step on slabs == the single domain, bit for bit."""
+    build_emu()
+    port = 31500 + (os.getpid() + world * 11) % 2000
+    mp.spawn(_worker_conc, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    h_want, C_want = _single_conc()
+    h = np.concatenate([np.load(tmp_path / f"h_{r}.npy") for r in range(world)], axis=2)
+    C = np.concatenate([np.load(tmp_path / f"C_{r}.npy") for r in range(world)], axis=2)
+    assert np.array_equal(h, h_want, equal_nan=True)
+    assert np.array_equal(C, C_want, equal_nan=True)
+    assert float(np.abs(C_want - 1.0).max()) > 1e-3   # the field is not trivially uniform
+
+
+@pytest.mark.skipif(have_cuda(), reason="CPU/gloo test of the host-side logic")
+@pytest.mark.parametrize("world", [2, 3])
+def test_moving_wall_slab_equals_single_domain(tmp_path, world):
+    """MRT + moving-wall reconstruction + INFLOW / OUTFLOW rows (the C3 step) on slabs == the single domain, bit for bit:
+    the wall step reads the pre-step velocity of neighbour rows, so rho / vel ghost rows are exchanged per step too."""
+    build_emu()
+    port = 33500 + (os.getpid() + world * 13) % 2000
+    mp.spawn(_worker_wall, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    want = dict(zip(("f", "rho", "vel"), _single_wall()))
+    for name, w in want.items():
+        got = np.concatenate([np.load(tmp_path / f"{name}_{r}.npy") for r in range(world)], axis=2)
+        assert np.array_equal(got, w, equal_nan=True), name
+    assert float(np.abs(want["vel"]).max()) > 1e-3
