@@ -120,6 +120,10 @@ typedef struct jrl_collide_desc
     const float *force;   /* [B,2,H,W] or NULL */
     const float *mesh_grid; /* [B,2,H,W] (cell centres) or NULL; required when axisym != 0 */
     float *f_out;         /* [B,9,H,W]; may alias f when axisym == 0 or is_convection */
+    /* Multi-GPU row slab, as in jrl_step_desc below: slab_rows == 0 = whole grid stored; slab_rows > 0 = every plane
+       is a local [slab_rows + 2, W] array (H stays the GLOBAL height) whose owned rows are collided; the axisymmetric
+       source reads rho / vel / flags / mesh_grid of the ghost rows, which the caller has exchanged. */
+    int slab_row0, slab_rows;
 } jrl_collide_desc;
 int jrl_collide_f32(const jrl_collide_desc *d, void *stream);
 

@@ -288,10 +288,18 @@ __global__ void __launch_bounds__(kThreads) k_collide(Grid g, const __grid_const
                                                       const float *__restrict__ f, const float *__restrict__ rho,
                                                       const float *__restrict__ vel, const uint8_t *__restrict__ flags,
                                                       const float *__restrict__ force, const float *__restrict__ mesh,
-                                                      float *__restrict__ f_out)
+                                                      float *__restrict__ f_out, int row0, int rows)
 {
     pdl_enter();
-    JRL_CELL_PROLOGUE
+    // global rows [row0, row0 + rows): the whole grid, or the owned rows of a row slab (cell() maps them to storage;
+    // whole grid: i == idx)
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)rows * g.W)
+        return;
+    const long long b = blockIdx.y;
+    const int y = row0 + (int)(idx / g.W);
+    const int x = (int)(idx - (long long)(y - row0) * g.W);
+    const long long i = cell(g, y, y, x);
     const float *s = f + b * 9 * g.HW + i;
     float *o = f_out + b * 9 * g.HW + i;
     float fc[9];
@@ -793,18 +801,29 @@ int jrl_collide_f32(const jrl_collide_desc *d, void *stream)
                 fn, "Please specific a right KBC Type value");
     JRL_REQUIRE(d->axisym == 0 || d->mesh_grid, fn, "axisymmetric collision needs mesh_grid");
     const bool stencil_src = d->axisym != 0 && !d->is_convection;
-    const Grid g = make_grid(d->H, d->W, d->axisym);
+    Grid g = make_grid(d->H, d->W, d->axisym);
+    int row0 = 0, rows = d->H;
+    if (d->slab_rows > 0)  // row slab: every plane is [slab_rows + 2, W]; the owned rows are collided, ghost rows only read
+    {
+        JRL_REQUIRE(d->slab_rows >= 3 && d->slab_row0 >= 0 && d->slab_row0 + d->slab_rows <= d->H, fn, "bad slab");
+        JRL_REQUIRE(d->f_out != d->f || !stencil_src, fn, "f_out must not alias f");
+        g.slab = 1;
+        g.y_off = d->slab_row0;
+        g.HW = (long long)(d->slab_rows + 2) * d->W;
+        row0 = d->slab_row0;
+        rows = d->slab_rows;
+    }
     CollideParams p;
     SourceParams sp;
     make_collide(p, sp, d->op, d->kbc_type, d->is_convection, d->axisym, d->dx, d->dt, d->tau, d->mrt);
     cudaStream_t s = (cudaStream_t)stream;
-    const dim3 grid = cell_grid(g, d->B);
+    const dim3 grid(blocks_for((long long)rows * d->W), (unsigned)d->B, 1);
 #define JRL_LAUNCH_COLLIDE(CONV, SRC)                                                                         \
     do                                                                                                        \
     {                                                                                                         \
         auto kern = k_collide<CONV, SRC>;                                                                     \
         JRL_LAUNCH_PDL(kern, grid, kThreads, s, g, p, sp, d->f, d->rho, d->vel, d->flags, d->force, d->mesh_grid, \
-                   d->f_out);                                                                                 \
+                   d->f_out, row0, rows);                                                                     \
     } while (0)
     if (d->is_convection)
     {

@@ -32,7 +32,7 @@ class CollideDesc(Structure):  # struct jrl_collide_desc
     _fields_ = [("B", c_int), ("H", c_int), ("W", c_int), ("axisym", c_int), ("op", c_int), ("kbc_type", c_int),
                 ("is_convection", c_int), ("dx", c_double), ("dt", c_double), ("tau", c_double),
                 ("mrt", c_void_p), ("f", c_void_p), ("rho", c_void_p), ("vel", c_void_p), ("flags", c_void_p),
-                ("force", c_void_p), ("mesh_grid", c_void_p), ("f_out", c_void_p)]
+                ("force", c_void_p), ("mesh_grid", c_void_p), ("f_out", c_void_p), ("slab_row0", c_int), ("slab_rows", c_int)]
 
 
 class StepDesc(Structure):  # struct jrl_step_desc

@@ -217,6 +217,7 @@ class SlabLattice:
         flags = args.pop("flags")
         rho, vel = args.pop("rho", None), args.pop("vel", None)
         store = args.pop("store_moments", False)
+        exchange = args.pop("exchange", True)   # False: the caller exchanges the ghost rows itself (AxisymFluidSlab)
         if store:  # the three launches of a step share one pair of moment buffers
             if "rho_out" not in args:
                 args["rho_out"] = self._moment_buffer("rho_out", 1)
@@ -244,7 +245,10 @@ class SlabLattice:
                 descs.append((d, keep))
             self._descs[key] = descs
         like = self.f
-        if self.overlap:
+        if not exchange:
+            for d, _ in descs:
+                N.call("jrl_step_f32", ctypes.byref(d), like=like)
+        elif self.overlap:
             # comm stream (high priority): edge rows -> pack -> NCCL p2p -> unpack; main stream: the interior, which
             # reads only owned rows of the previous step and writes rows the edge launches do not touch, so the two
             # run side by side.  (Until round 2 the edge launches sat on the main stream IN FRONT of the interior:
@@ -269,3 +273,45 @@ class SlabLattice:
             self.exchange(self.f_next)
         self.f, self.f_next = self.f_next, self.f
         return self.f
+
+
+class AxisymFluidSlab:
+    """JRL stage A -- the axisymmetric FLUID step (demo_2d_LBM_JRL_fluid_cylinder.py:216-247) -- on row slabs.
+
+    Its collision source takes gradients of the NEW moments (LBM_collision_2d.py:386-427), so the step is two passes with
+    an exchange in between ("stage A"):
+
+        1. streaming + moving wall + moments in one fused pass (JRL_OP_NONE) on the owned rows -> f', rho', vel'
+        2. ghost rows of rho', vel' from the neighbours (the source's 3 x 3 stencils; next step's wall reads vel' too)
+        3. collision with the axisymmetric source on the owned rows (jrl_collide_f32, slab form) -> f"
+        4. ghost rows of f" for the next step's streaming
+
+    `lat`: a SlabLattice over a FusedStep built with operator="none" and the stage's axisymmetric_type; `collision`: the
+    LBMCollision2d of the same SimulationRunner.  Bit-identical to the single domain (tests/test_slab_gloo.py, world 2
+    and 3 over gloo); not yet timed on GPUs -- all four stages run back to back on the current stream."""
+
+    def __init__(self, lat, collision, dx=1.0, dt=1.0):
+        if lat.fs.op != N.OP_NONE:
+            raise RuntimeError("AxisymFluidSlab needs a SlabLattice over FusedStep(operator='none')")
+        self.lat, self.col, self.dx, self.dt = lat, collision, float(dx), float(dt)
+        self._f_post = None
+
+    def step(self, rho, vel, mesh_grid, force=None, **kw):
+        """rho, vel: slab tensors of the previous step's moments with valid ghost rows; mesh_grid (cell centres) and force
+        (density * gravity, or None) slabs go to the collision only, as in the demo.  Per-step fields of the first pass
+        (flags, phi_obs, obs_vel, ...) by keyword as in SlabLattice.step, or once through set_state.  Returns the new
+        (rho, vel) slabs, ghost rows exchanged; the new populations are lat.f."""
+        lat = self.lat
+        lat.step(rho=rho, vel=vel, store_moments=True, exchange=False, **kw)
+        rho_new, vel_new = lat._staging["rho_out"].clone(), lat._staging["vel_out"].clone()
+        lat.exchange(rho_new)
+        lat.exchange(vel_new)
+        args = dict(lat.fields)
+        args.update(kw)
+        op, kbc, tau = self.col._operator(False, None)
+        f_post = lat.f_next   # the buffer the previous populations lived in: free until the next streaming pass
+        self.col._collide(self.dx, self.dt, lat.f, rho_new, vel_new, args["flags"], force, mesh_grid, False, op, kbc, tau,
+                          slab=(lat.row0, lat.nrows, lat.H), f_out=f_post)
+        lat.f, lat.f_next = f_post, lat.f
+        lat.exchange(lat.f)
+        return rho_new, vel_new

@@ -396,10 +396,17 @@ class LBMCollision2d:
             else:
                 L._why(why)
         f, rho, vel, flags, force, mesh_grid = (resolve(t) for t in (f, rho, vel, flags, force, mesh_grid))
+        return self._collide(dx, dt, f, rho, vel, flags, force, mesh_grid, is_convection, op, kbc, tau)
+
+    def _collide(self, dx, dt, f, rho, vel, flags, force, mesh_grid, is_convection, op, kbc, tau, slab=None, f_out=None):
+        """One launch of jrl_collide_f32 on ordinary tensors.  slab = (row0, nrows, H_global): the tensors are row slabs
+        [.., nrows + 2, W] with exchanged ghost rows (jrl_slab.AxisymFluidSlab); only the owned rows of f_out are written."""
         B, H, W = _dims(f)
         force = _full(force, (B, 2, H, W), "force", f)
         d = N.CollideDesc()
         d.B, d.H, d.W = B, H, W
+        if slab is not None:
+            d.slab_row0, d.slab_rows, d.H = int(slab[0]), int(slab[1]), int(slab[2])
         d.axisym = self.axisymmetric_type
         d.op, d.kbc_type, d.is_convection = op, kbc, int(bool(is_convection))
         d.dx, d.dt, d.tau = float(dx), float(dt), float(tau)
@@ -410,8 +417,9 @@ class LBMCollision2d:
         d.flags = N.tensor_ptr(flags, "flags", torch.uint8, (B, 1, H, W), like=f)
         d.force = N.tensor_ptr(force, "force", shape=(B, 2, H, W), like=f, optional=True)
         d.mesh_grid = N.tensor_ptr(mesh_grid, "mesh_grid", shape=(B, 2, H, W), like=f, optional=True)
-        f_out = torch.empty_like(f)
-        d.f_out = f_out.data_ptr()
+        if f_out is None:
+            f_out = torch.empty_like(f)
+        d.f_out = N.tensor_ptr(f_out, "f_out", shape=(B, 9, H, W), like=f)
         N.call("jrl_collide_f32", ctypes.byref(d), like=f)
         return f_out
 
