@@ -13,15 +13,15 @@ Per step (CUDA):   comm stream : wait for main, update the two edge rows (one la
 The exchange moves 2 x 9 x W fp32 per rank per step (2.4 MB at W = 32768) against
 72 B x nrows x W of HBM traffic for the interior, so it hides completely behind the interior.
 
-A slab step is ~10 stream operations (three step launches with their work-list passes, pack / NCCL send-recv /
-unpack) issued from Python: ~150 us of host time, which the 1.7 ms interior of the 32768^2 grid hides but the 170 us
-step of the 8192^2 concentration grid on 8 GPUs does not (66 % strong-scaling efficiency in round 1).  `step()`
-can therefore capture the whole step -- both streams and the NCCL point-to-point calls -- into a CUDA graph per
-ping-pong parity once the same call has been seen twice, and replay it: one graph launch per step.
-OFF by default (JRL_SLAB_GRAPH=1 enables it).  With it on the slab run is bit-exact against the single domain
-(tools/check_slab_nccl.py at N = 2), but the captured graphs hold NCCL operations: `release_all_graphs()` (or
-`SlabLattice.close()`) MUST run before `dist.destroy_process_group()`, which otherwise never returns -- the reason
-the first run made with it did not finish.  The eager path is the one the committed scaling numbers were taken on.
+A slab step is ~15 host calls (three step launches with their work-list passes, pack / NCCL send-recv / unpack, stream
+switches) issued from Python: ~200 us of host time, which the 1.7 ms interior of the 32768^2 grid hides but the 185 us
+of kernels of the 8192^2 concentration grid on 8 GPUs do not.  `step()` can therefore capture the whole step -- both
+streams and the NCCL point-to-point calls -- into a CUDA graph per ping-pong parity once the same call has been seen
+twice, and replay it: one graph launch per step (1024 x 8192 per rank: 0.229 -> 0.202 ms; profiles/r2_slab_trace.md).
+OFF by default (`graph=True` or JRL_SLAB_GRAPH=1 enables it; bench.py's C4 slab does).  The replayed run is bit-exact
+against the single domain (tools/check_slab_nccl.py at N = 2), but the captured graphs hold NCCL operations:
+`release_all_graphs()` (or `SlabLattice.close()`) MUST run before `dist.destroy_process_group()`, which otherwise never
+returns.  `AxisymFluidSlab` (below) runs JRL stage A's two-pass step on the same slabs.
 """
 from __future__ import annotations
 
