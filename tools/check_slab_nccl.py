@@ -27,6 +27,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--grid", type=int, default=2048)
     ap.add_argument("--steps", type=int, default=12)
+    ap.add_argument("--stage-a", action="store_true", help="also check jrl_slab.AxisymFluidSlab (not yet run on GPUs)")
     args = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     if os.environ.get("JRL_DEBUG_HANG"):  # print every thread's stack and exit if the check has not finished by then
@@ -81,6 +82,39 @@ def main():
         t = torch.tensor([0 if same else 1], device=dev)
         dist.all_reduce(t)
         report[kind] = "bit-exact" if t.item() == 0 else f"MISMATCH on {int(t.item())} rank(s)"
+        bad += int(t.item())
+    # JRL stage A's two-pass step on slabs (jrl_slab.AxisymFluidSlab) against the single domain's two launches: the
+    # problem of tests/test_slab_gloo.py (seeded random state with every CellType, x-axis symmetry, moving wall, gravity)
+    if args.stage_a:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        Hc, Wc = 36 * world, 2048
+        st = S.random_state((Hc, Wc), 9, dev, axisym=1)
+        P = api.SimulationParameters(simulation_size=(1, 1, Hc, Wc), device=dev, tau=0.8, contact_angle=None, axisymmetric_type=1,
+                                     gravity_strength=2e-5)
+        R = api.SimulationRunner(P)
+        col = R.create_collision()
+        col.preset_KBC(dx=1.0, dt=1.0, tau=0.8)
+        fs = R.create_fused_step(operator="none")
+        mesh = api.create_2d_meshgrid_tensor(size=(1, 1, Hc, Wc), device=dev, dtype=torch.float32) + 0.5
+        op, kbc, tau = col._operator(False, None)
+        f, r1, v1 = st["f"], st["rho"], st["vel"]
+        for _ in range(args.steps):
+            f1, r1, v1 = fs.step(f, st["flags"], r1, v1, phi_obs=st["phi"], use_wall=True, obs_vel=st["obs_vel"], inflow_density=1.0)
+            f = col._collide(1.0, 1.0, f1, r1, v1, st["flags"], st["force"], mesh, False, op, kbc, tau)
+        lat = jrl_slab.SlabLattice(fs, Hc, Wc, device=dev)
+        lat.set_state(lat.scatter_global(st["f"]), flags=lat.scatter_global(st["flags"]), phi_obs=lat.scatter_global(st["phi"]),
+                      use_wall=True, obs_vel=lat.scatter_global(st["obs_vel"]), inflow_density=1.0)
+        stage = jrl_slab.AxisymFluidSlab(lat, col)
+        r, v = lat.scatter_global(st["rho"]), lat.scatter_global(st["vel"])
+        mesh_s, force_s = lat.scatter_global(mesh), lat.scatter_global(st["force"])
+        for _ in range(args.steps):
+            r, v = stage.step(r, v, mesh_s, force=force_s)
+        torch.cuda.synchronize()
+        mine, want = lat.owned(lat.f), f[:, :, lat.row0:lat.row0 + lat.nrows, :]
+        same = bool(((mine == want) | (mine.isnan() & want.isnan())).all())
+        t = torch.tensor([0 if same else 1], device=dev)
+        dist.all_reduce(t)
+        report["stage_a"] = "bit-exact" if t.item() == 0 else f"MISMATCH on {int(t.item())} rank(s)"
         bad += int(t.item())
     if rank == 0:
         print(json.dumps(report), flush=True)
