@@ -41,7 +41,10 @@ def pytest_collection_modifyitems(config, items):
 
 
 def build_emu():
-    """tests/host_emu: the kernel sources of jrl-lbm_b200/csrc compiled for the host (test-only)."""
+    """tests/host_emu: the kernel sources of jrl-lbm_b200/csrc compiled for the host (test-only).
+    JRL_EMU_LIB in the environment substitutes another build of the same sources (tools/sanitize_emu.sh: ASan + UBSan)."""
+    if os.environ.get("JRL_EMU_LIB"):
+        return os.environ["JRL_EMU_LIB"]
     srcs = [os.path.join(PKG, "csrc", f) for f in os.listdir(os.path.join(PKG, "csrc"))]
     srcs += [os.path.join(ROOT, "include", "jrl_lbm.h"), os.path.join(ROOT, "tests", "host_emu", "cuda_runtime.h")]
     if not os.path.exists(EMU_LIB) or os.path.getmtime(EMU_LIB) < max(os.path.getmtime(s) for s in srcs):
