@@ -211,3 +211,77 @@ def test_concentration_chain_clamp_spellings_emu(emu_api, spelling, axisym):
             L.ENABLED = True
     for a, b in zip(*outs):
         assert np.array_equal(a, b, equal_nan=True), spelling
+
+
+WALL_ACTIONS = ["none"] * 6 + ["read_wall_f", "inplace_wall_f", "clone_wall_f", "read_vel_in", "skip_wall", "wall_twice", "read_rho",
+                               "stale_stream_after"]
+
+
+def _wall_program(api, seed, enabled):
+    """The four-call chain WITH solve_boundary (demo_2d_LBM_cylinder.py:138-172; stage A's axisymmetric form in a third of
+    the programs), MRT / KBC / BGK collision objects, and user actions around the wall call."""
+    rng = random.Random(1000 + seed)
+    L.ENABLED = enabled
+    try:
+        axisym = 1 if rng.random() < 0.35 else 0
+        kind = "bgk" if axisym else rng.choice(["bgk", "mrt", "kbc"])
+        P = api.SimulationParameters(dim=2, dtype=torch.float32, device=DEV, simulation_size=(1, 1, H, W), dt=1.0,
+                                     contact_angle=None, Q=9, tau=0.8, axisymmetric_type=axisym, gravity_strength=1e-5)
+        R = api.SimulationRunner(parameters=P)
+        prop, macro, wall = R.create_propagation(), R.create_macro_compute(), R.create_LBM_fluid_solid_coupling()
+        col = {"bgk": R.create_collision, "mrt": R.create_collision_MRT, "kbc": R.create_collision_KBC}[kind]()
+        col.preset_KBC(dx=1.0, dt=1.0, tau=0.8)
+        s = S.random_state((H, W), 20 + seed % 5, DEV, axisym)
+        mesh = api.create_2d_meshgrid_tensor(size=(1, 1, H, W), device=DEV, dtype=torch.float32) + 0.5
+        f, flags, rho, vel, phi, obs_vel = s["f"], s["flags"], s["rho"], s["vel"], s["phi"], s["obs_vel"]
+        force = s["force"] if rng.random() < 0.5 else None
+        kbc_type = int(rng.choice([api.KBCType.KBC_C, api.KBCType.KBC_D, api.KBCType.LBGK])) if kind == "kbc" else int(api.KBCType.KBC_C)
+        seen, used = [], set()
+
+        def obs(x):
+            seen.append(np.asarray(x.detach().cpu().numpy()).copy())
+
+        for step in range(rng.randint(2, 3)):
+            rho_in, vel_in, f1 = prop.propagation(f=f, flags=flags, phi_obs=phi, rho=rho, vel=vel, inflow_density=1.0,
+                                                  inflow_vel=torch.tensor([0.0, 0.02]))
+            a = rng.choice(WALL_ACTIONS)
+            used.add(a)
+            if a == "read_vel_in":
+                obs(vel_in[0, :, 2])
+            if a == "skip_wall":
+                f2 = f1
+            else:
+                f2 = wall.solve_boundary(dt=1.0, dx=1.0, rho=rho_in, vel=vel_in, flags=flags, f=f1, phi_obs=phi, obs_vel=obs_vel, tau=0.8)
+                if a == "wall_twice":
+                    f2 = wall.solve_boundary(dt=1.0, dx=1.0, rho=rho_in, vel=vel_in, flags=flags, f=f2, phi_obs=phi, obs_vel=obs_vel, tau=0.8)
+            if a == "read_wall_f":
+                obs(f2[0, 5])
+            elif a == "inplace_wall_f":
+                f2[:, 2, 1, 1] -= 0.002
+            elif a == "clone_wall_f":
+                f2 = f2.clone()
+            rho, vel = macro.macro_compute(dx=1.0, dt=1.0, f=f2, rho=rho_in, vel=vel_in, flags=flags)
+            if a == "read_rho":
+                obs(rho.min())
+            f = col.collision(dx=1.0, dt=1.0, f=f2, rho=rho, vel=vel, flags=flags, force=force,
+                              mesh_grid=mesh if axisym else None, KBC_type=kbc_type)
+            if a == "stale_stream_after":
+                obs(f1[0, 1, 3])         # the pre-wall streamed populations, after the fused step has run
+        return seen, [np.asarray(t.detach().cpu().numpy()).copy() for t in (f, rho, vel)], used
+    finally:
+        L.ENABLED = True
+
+
+@pytest.mark.parametrize("block", range(3))
+def test_random_wall_chain_programs_emu(emu_api, block):
+    fused0 = L.stats["fused"]
+    for seed in range(block * 15, block * 15 + 15):
+        want_seen, want_final, used = _wall_program(emu_api, seed, enabled=False)
+        got_seen, got_final, _ = _wall_program(emu_api, seed, enabled=True)
+        assert len(want_seen) == len(got_seen), f"program {seed}"
+        for i, (a, b) in enumerate(zip(want_seen, got_seen)):
+            assert np.array_equal(a, b, equal_nan=True), f"wall program {seed}: observation {i} differs ({sorted(used)})"
+        for i, (a, b) in enumerate(zip(want_final, got_final)):
+            assert np.array_equal(a, b, equal_nan=True), f"wall program {seed}: final field {i} differs ({sorted(used)})"
+    print(f"block {block}: 15 wall-chain programs, {L.stats['fused'] - fused0} steps fused")
+    assert L.stats["fused"] - fused0 >= 5
