@@ -1,0 +1,60 @@
+"""Random four-call chains (tests/test_lazy_user_programs.py: BGK / MRT / KBC C, D, LBGK, with and without solve_boundary,
+x-axis symmetric stage-A form, forces, inflow, user actions in between) on the PRODUCT -- deferred chain, host-emulated
+kernels -- against the ORACLE's restatement of the reference behind the same solver-object API (oracle/oracle_api.py).
+The lazy-layer tests compare the product with itself (deferred vs immediate); this one closes the loop to the reference's
+arithmetic: <= 1e-5 relative L2 on every observation and final field (BASELINE north_star), bit-identical reported."""
+import numpy as np
+import pytest
+
+from test_lazy_user_programs import _wall_program
+from util import REL_L2_TOL, rel_l2
+
+
+@pytest.mark.parametrize("block", range(3))
+def test_random_wall_chains_match_oracle(emu_api, oracle_api, block):
+    exact = total = 0
+    for seed in range(block * 15, block * 15 + 15):
+        want_seen, want_final, used = _wall_program(oracle_api, seed, enabled=False)
+        got_seen, got_final, _ = _wall_program(emu_api, seed, enabled=True)
+        assert len(want_seen) == len(got_seen)
+        for what, ws, gs in (("observation", want_seen, got_seen), ("final field", want_final, got_final)):
+            for i, (w, g) in enumerate(zip(ws, gs)):
+                w, g = np.asarray(w, np.float64), np.asarray(g, np.float64)
+                assert np.array_equal(np.isfinite(w), np.isfinite(g)), f"program {seed}: {what} {i}: finite masks differ"
+                m = np.isfinite(w)
+                e = rel_l2(g[m], w[m]) if m.any() and np.abs(w[m]).max() > 0 else float(np.abs(g[m] - w[m]).max(initial=0.0))
+                assert e <= REL_L2_TOL, f"program {seed}: {what} {i} differs from the oracle by {e:.3e} ({sorted(used)})"
+                total += 1
+                exact += int(np.array_equal(w, g, equal_nan=True))
+    print(f"block {block}: {exact} of {total} arrays bit-identical to the oracle")
+
+
+@pytest.mark.parametrize("block", range(2))
+def test_random_plain_chains_match_oracle(emu_api, oracle_api, block):
+    """The three-call chain programs (two interleaved solver sets, inflow, in-place user writes) against the oracle; programs
+    that write into a recorded input raise in the deferred run by design and are skipped here."""
+    from test_lazy_user_programs import _program
+    exact = total = skipped = 0
+    for seed in range(block * 20, block * 20 + 20):
+        want_seen, want_final, used = _program(oracle_api, seed, enabled=False)
+        try:
+            got_seen, got_final, _ = _program(emu_api, seed, enabled=True)
+        except RuntimeError as e:
+            assert "modified in place" in str(e)
+            skipped += 1
+            continue
+        assert len(want_seen) == len(got_seen)
+        for what, ws, gs in (("observation", want_seen, got_seen), ("final field", want_final, got_final)):
+            for i, (w, g) in enumerate(zip(ws, gs)):
+                if np.asarray(w).dtype.kind in "iub":
+                    assert np.array_equal(w, g), f"program {seed}: {what} {i} (integer) differs"
+                    continue
+                w, g = np.asarray(w, np.float64), np.asarray(g, np.float64)
+                assert np.array_equal(np.isfinite(w), np.isfinite(g)), f"program {seed}: {what} {i}: finite masks differ"
+                m = np.isfinite(w)
+                e = rel_l2(g[m], w[m]) if m.any() and np.abs(w[m]).max() > 0 else float(np.abs(g[m] - w[m]).max(initial=0.0))
+                assert e <= REL_L2_TOL, f"program {seed}: {what} {i} differs from the oracle by {e:.3e} ({sorted(used)})"
+                total += 1
+                exact += int(np.array_equal(w, g, equal_nan=True))
+    print(f"block {block}: {exact} of {total} arrays bit-identical to the oracle, {skipped} programs skipped (documented error)")
+    assert skipped <= 10
