@@ -217,22 +217,23 @@ WALL_ACTIONS = ["none"] * 6 + ["read_wall_f", "inplace_wall_f", "clone_wall_f", 
                                "stale_stream_after"]
 
 
-def _wall_program(api, seed, enabled):
+def _wall_program(api, seed, enabled, hw=None):
     """The four-call chain WITH solve_boundary (demo_2d_LBM_cylinder.py:138-172; stage A's axisymmetric form in a third of
     the programs), MRT / KBC / BGK collision objects, and user actions around the wall call."""
     rng = random.Random(1000 + seed)
+    Hh, Ww = hw or (H, W)   # other extents reach the 1- and 4-cell-per-thread kernels (W odd / W % 4 == 0)
     L.ENABLED = enabled
     try:
         axisym = 1 if rng.random() < 0.35 else 0
         kind = "bgk" if axisym else rng.choice(["bgk", "mrt", "kbc"])
-        P = api.SimulationParameters(dim=2, dtype=torch.float32, device=DEV, simulation_size=(1, 1, H, W), dt=1.0,
+        P = api.SimulationParameters(dim=2, dtype=torch.float32, device=DEV, simulation_size=(1, 1, Hh, Ww), dt=1.0,
                                      contact_angle=None, Q=9, tau=0.8, axisymmetric_type=axisym, gravity_strength=1e-5)
         R = api.SimulationRunner(parameters=P)
         prop, macro, wall = R.create_propagation(), R.create_macro_compute(), R.create_LBM_fluid_solid_coupling()
         col = {"bgk": R.create_collision, "mrt": R.create_collision_MRT, "kbc": R.create_collision_KBC}[kind]()
         col.preset_KBC(dx=1.0, dt=1.0, tau=0.8)
-        s = S.random_state((H, W), 20 + seed % 5, DEV, axisym)
-        mesh = api.create_2d_meshgrid_tensor(size=(1, 1, H, W), device=DEV, dtype=torch.float32) + 0.5
+        s = S.random_state((Hh, Ww), 20 + seed % 5, DEV, axisym)
+        mesh = api.create_2d_meshgrid_tensor(size=(1, 1, Hh, Ww), device=DEV, dtype=torch.float32) + 0.5
         f, flags, rho, vel, phi, obs_vel = s["f"], s["flags"], s["rho"], s["vel"], s["phi"], s["obs_vel"]
         force = s["force"] if rng.random() < 0.5 else None
         kbc_type = int(rng.choice([api.KBCType.KBC_C, api.KBCType.KBC_D, api.KBCType.LBGK])) if kind == "kbc" else int(api.KBCType.KBC_C)
