@@ -46,7 +46,8 @@ def build_emu():
     if os.environ.get("JRL_EMU_LIB"):
         return os.environ["JRL_EMU_LIB"]
     srcs = [os.path.join(PKG, "csrc", f) for f in os.listdir(os.path.join(PKG, "csrc"))]
-    srcs += [os.path.join(ROOT, "include", "jrl_lbm.h"), os.path.join(ROOT, "tests", "host_emu", "cuda_runtime.h")]
+    srcs += [os.path.join(ROOT, "include", "jrl_lbm.h"), os.path.join(ROOT, "tests", "host_emu", "cuda_runtime.h"),
+             os.path.join(ROOT, "tests", "host_emu", "emu_globals.cpp")]
     if not os.path.exists(EMU_LIB) or os.path.getmtime(EMU_LIB) < max(os.path.getmtime(s) for s in srcs):
         subprocess.run(["bash", os.path.join(ROOT, "tests", "host_emu", "build.sh")], check=True,
                        stdout=subprocess.DEVNULL)

@@ -55,27 +55,39 @@ using std::max;
 using std::min;
 
 namespace jrl_emu {
+// JRL_EMU_REVERSE (tests/test_emu_order_independence.py): blocks and threads run serially in DESCENDING order instead
+// of ascending / OpenMP-parallel.  A kernel whose result depends on the order in which its threads run -- a thread reading
+// what another thread of the same launch writes, like the reference's OUTFLOW rows (propagation.cu:195-255) -- gives
+// different bits in the two builds.
 template <typename F>
 void launch(dim3 grid, dim3 block, F body)
 {
     const long long nblocks = (long long)grid.x * grid.y * grid.z;
+#ifdef JRL_EMU_REVERSE
+    for (long long bi = nblocks - 1; bi >= 0; --bi)
+#else
 #pragma omp parallel for schedule(static)
     for (long long bi = 0; bi < nblocks; ++bi)
+#endif
     {
         gridDim = grid;
         blockDim = block;
         blockIdx.x = (unsigned)(bi % grid.x);
         blockIdx.y = (unsigned)((bi / grid.x) % grid.y);
         blockIdx.z = (unsigned)(bi / ((long long)grid.x * grid.y));
-        for (unsigned tz = 0; tz < block.z; ++tz)
-            for (unsigned ty = 0; ty < block.y; ++ty)
-                for (unsigned tx = 0; tx < block.x; ++tx)
-                {
-                    threadIdx.x = tx;
-                    threadIdx.y = ty;
-                    threadIdx.z = tz;
-                    body();
-                }
+        const long long nthreads = (long long)block.x * block.y * block.z;
+        for (long long k = 0; k < nthreads; ++k)
+        {
+#ifdef JRL_EMU_REVERSE
+            const long long t = nthreads - 1 - k;
+#else
+            const long long t = k;
+#endif
+            threadIdx.x = (unsigned)(t % block.x);
+            threadIdx.y = (unsigned)((t / block.x) % block.y);
+            threadIdx.z = (unsigned)(t / ((long long)block.x * block.y));
+            body();
+        }
     }
 }
 }  // namespace jrl_emu
